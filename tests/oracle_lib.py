@@ -1,0 +1,134 @@
+"""ctypes doors into the CHECKERS: oracle/liboracle.so (our C restatement) and,
+when it has been built, oracle/_ref/libhavac_ref.so (the unmodified reference
+objects). Only tests/, __graft_entry__.smoke() and bench.py's CPU legs import
+this module; nothing under havac_b200/ does."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+_u8p = np.ctypeslib.ndpointer(np.uint8, flags="C")
+_i8p = np.ctypeslib.ndpointer(np.int8, flags="C")
+_u64p = np.ctypeslib.ndpointer(np.uint64, flags="C")
+_u32p = np.ctypeslib.ndpointer(np.uint32, flags="C")
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C")
+
+
+def build_oracle():
+    subprocess.run(["make", "-C", ORACLE_DIR, "-s"], check=True, stdout=subprocess.DEVNULL)
+
+
+def _load(path):
+    return C.CDLL(path) if os.path.exists(path) else None
+
+
+_oracle = None
+_ref = None
+
+
+def oracle():
+    global _oracle
+    if _oracle is None:
+        p = os.path.join(ORACLE_DIR, "liboracle.so")
+        if not os.path.exists(p):
+            build_oracle()
+        L = C.CDLL(p)
+        L.oracle_soft_ssv.restype = C.c_int64
+        L.oracle_soft_ssv.argtypes = [_u8p, C.c_uint64, _i8p, C.c_uint64, _u64p, _u32p, C.c_uint64]
+        L.oracle_replay_diagonal.restype = C.c_int64
+        L.oracle_replay_diagonal.argtypes = [_u8p, C.c_uint64, _i8p, C.c_uint64, C.c_int64, _u32p, C.c_uint64]
+        L.oracle_unpack_2bit.argtypes = [_u8p, C.c_uint64, _u8p]
+        L.oracle_pack_2bit.argtypes = [_u8p, C.c_uint64, _u8p]
+        L.oracle_encode_hit.restype = C.c_uint64
+        L.oracle_encode_hit.argtypes = [C.c_uint64, C.c_uint32]
+        L.oracle_resolve_hit.restype = C.c_int
+        L.oracle_resolve_hit.argtypes = [C.c_uint64, _u64p, C.c_uint64, _u32p, C.c_uint32,
+                                         C.POINTER(C.c_uint64), C.POINTER(C.c_uint32),
+                                         C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+        L.oracle_cell_processor.argtypes = [C.c_uint8, C.c_int8, C.POINTER(C.c_uint8), C.POINTER(C.c_int)]
+        L.oracle_gumbel_invsurv.restype = C.c_double
+        L.oracle_gumbel_invsurv.argtypes = [C.c_double, C.c_double, C.c_double]
+        L.oracle_scale_factor.restype = C.c_float
+        L.oracle_scale_factor.argtypes = [C.c_float, C.c_float, C.c_uint32, C.c_uint32, C.c_float]
+        L.oracle_project_model.argtypes = [_f32p, C.c_uint32, C.c_float, _i8p]
+        _oracle = L
+    return _oracle
+
+
+def ref():
+    """The compiled reference, or None where it has not been built (GPU box
+    without a prebuilt oracle/_ref)."""
+    global _ref
+    if _ref is None:
+        p = os.path.join(ORACLE_DIR, "_ref", "libhavac_ref.so")
+        if not os.path.exists(p) and os.path.isdir("/root/reference/test/softSsv"):
+            build_oracle()
+        L = _load(p)
+        if L is None:
+            return None
+        L.ref_soft_ssv.restype = C.c_int64
+        L.ref_soft_ssv.argtypes = [_u8p, C.c_uint64, _i8p, C.c_uint64, _u64p, _u32p, C.c_uint64]
+        L.ref_scale_factor.restype = C.c_float
+        L.ref_scale_factor.argtypes = [C.c_float, C.c_float, C.c_uint32, C.c_uint32, C.c_float]
+        L.ref_load_phmm.restype = C.c_int64
+        L.ref_load_phmm.argtypes = [C.c_char_p, C.c_float, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32,
+                                    C.POINTER(C.c_uint32)]
+        L.ref_load_fasta.restype = C.c_int64
+        L.ref_load_fasta.argtypes = [C.c_char_p, C.c_uint, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                     C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.ref_local_position.restype = C.c_int
+        L.ref_local_position.argtypes = [_u64p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64),
+                                         C.POINTER(C.c_uint64)]
+        _ref = L
+    return _ref
+
+
+# ---- numpy-friendly wrappers -------------------------------------------------
+
+def soft_ssv(symbols, table, lib=None, cap=1 << 22):
+    """Run the SSV recurrence; returns (seqPos u64[], row u32[])."""
+    L = lib or oracle()
+    fn = L.oracle_soft_ssv if hasattr(L, "oracle_soft_ssv") else L.ref_soft_ssv
+    symbols = np.ascontiguousarray(symbols, dtype=np.uint8)
+    table = np.ascontiguousarray(table, dtype=np.int8).reshape(-1)
+    pos = np.zeros(cap, dtype=np.uint64)
+    row = np.zeros(cap, dtype=np.uint32)
+    n = fn(symbols, len(symbols), table, len(table) // 4, pos, row, cap)
+    if n < 0 or n > cap:
+        raise RuntimeError(f"soft ssv failed or overflowed: {n}")
+    return pos[:n].copy(), row[:n].copy()
+
+
+def encode_hits(pos, row):
+    pos = np.asarray(pos, dtype=np.uint64)
+    row = np.asarray(row, dtype=np.uint64)
+    seg = pos // np.uint64(12288)
+    cell = pos % np.uint64(12288)
+    return cell | (seg << np.uint64(14)) | (row << np.uint64(40))
+
+
+def ref_load_phmm(path, p):
+    L = ref()
+    n = C.c_uint32(0)
+    rows = L.ref_load_phmm(path.encode(), p, None, 0, None, 0, C.byref(n))
+    if rows < 0:
+        raise RuntimeError(f"reference readP7Hmm failed on {path}: {rows}")
+    table = np.zeros(rows * 4, dtype=np.int8)
+    lens = np.zeros(n.value, dtype=np.uint32)
+    L.ref_load_phmm(path.encode(), p, table.ctypes.data, table.nbytes, lens.ctypes.data, n.value, C.byref(n))
+    return table, lens
+
+
+def ref_load_fasta(path, seed=1):
+    L = ref()
+    ns, cnt = C.c_uint64(0), C.c_uint64(0)
+    nb = L.ref_load_fasta(path.encode(), seed, None, 0, None, 0, C.byref(ns), C.byref(cnt))
+    if nb < 0:
+        raise RuntimeError(f"reference fastaVectorReadFasta failed on {path}: {nb}")
+    packed = np.zeros(nb, dtype=np.uint8)
+    ends = np.zeros(ns.value, dtype=np.uint64)
+    L.ref_load_fasta(path.encode(), seed, packed.ctypes.data, nb, ends.ctypes.data, ns.value, C.byref(ns), C.byref(cnt))
+    return packed, ends, cnt.value
