@@ -1,0 +1,181 @@
+"""ctypes binding of the C-ABI device client (include/havac_cuda.h).
+
+`HavacHwClient` mirrors the reference class of the same name method for method
+(host/HavacHwClient.hpp:21-115): writeSequence, writePhmm, invokeHavacSsvAsync,
+getHwState, waitForHavacSsvAsync, abort, getHitList -- with the same error
+behaviour mapped onto Python exceptions (length_error -> ValueError,
+logic_error -> RuntimeError subclass LogicError, runtime_error -> RuntimeError,
+bad_alloc -> MemoryError). There is no CPU fallback: if the CUDA library is
+missing or no sm_100 device is present, construction raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+from . import build
+
+OK = 0
+E_INVALID, E_LENGTH, E_LOGIC, E_RUNTIME, E_NOMEM, E_NODEVICE, E_OVERFLOW = -1, -2, -3, -4, -5, -6, -7
+STATE_NEW, STATE_QUEUED, STATE_RUNNING, STATE_COMPLETED, STATE_ERROR, STATE_ABORT, STATE_SUBMITTED, \
+    STATE_TIMEOUT, STATE_NORESPONSE = range(1, 10)
+SEGMENT_SYMBOLS = 12288
+
+EXPORTS = [
+    "havac_cuda_create", "havac_cuda_destroy", "havac_cuda_write_sequence", "havac_cuda_write_phmm",
+    "havac_cuda_set_segment_range", "havac_cuda_invoke_async", "havac_cuda_state", "havac_cuda_wait",
+    "havac_cuda_abort", "havac_cuda_num_hits", "havac_cuda_read_hits", "havac_cuda_last_error",
+    "havac_cuda_device_time_ms", "havac_cuda_device_count", "havac_cuda_run_stats", "havac_cuda_set_kernel",
+]
+
+
+class LogicError(RuntimeError):
+    """std::logic_error of the reference (calls made out of order)."""
+
+
+class HitOverflowError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library(path: Optional[str] = None) -> C.CDLL:
+    """Load libhavac_cuda.so (no GPU needed just to load it). Fails loudly when absent."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or build.CUDA_LIB
+    if not os.path.exists(p):
+        raise RuntimeError(f"{p} is missing: build it with `python -m havac_b200.build` "
+                           "(there is no CPU fallback for the SSV path)")
+    L = C.CDLL(p)
+    vp, u64, u32 = C.c_void_p, C.c_uint64, C.c_uint32
+    L.havac_cuda_create.argtypes = [C.c_char_p, u32, C.POINTER(vp)]
+    L.havac_cuda_destroy.argtypes = [vp]
+    L.havac_cuda_write_sequence.argtypes = [vp, vp, u64]
+    L.havac_cuda_write_phmm.argtypes = [vp, vp, u64]
+    L.havac_cuda_set_segment_range.argtypes = [vp, u64, u64]
+    L.havac_cuda_invoke_async.argtypes = [vp]
+    L.havac_cuda_state.argtypes = [vp, C.POINTER(C.c_int)]
+    L.havac_cuda_wait.argtypes = [vp, u64, C.POINTER(C.c_int)]
+    L.havac_cuda_abort.argtypes = [vp, C.POINTER(C.c_int)]
+    L.havac_cuda_num_hits.argtypes = [vp, C.POINTER(u64)]
+    L.havac_cuda_read_hits.argtypes = [vp, vp, u64, C.POINTER(u64)]
+    L.havac_cuda_last_error.argtypes = [vp]
+    L.havac_cuda_last_error.restype = C.c_char_p
+    L.havac_cuda_device_time_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    L.havac_cuda_device_count.argtypes = [vp, C.POINTER(C.c_int)]
+    L.havac_cuda_run_stats.argtypes = [vp, C.POINTER(u64), C.POINTER(u32)]
+    L.havac_cuda_set_kernel.argtypes = [vp, C.c_char_p]
+    for name in EXPORTS:
+        if name != "havac_cuda_last_error":
+            getattr(L, name).restype = C.c_int
+    if path is None:
+        _lib = L
+    return L
+
+
+class HavacHwClient:
+    def __init__(self, xclbinFileSrc: str = "", havacKernelName: str = "HavacKernel", deviceIndex: int = 0):
+        self._L = load_library()
+        self._h = C.c_void_p()
+        rc = self._L.havac_cuda_create((xclbinFileSrc or "").encode(), deviceIndex, C.byref(self._h))
+        if rc != OK:
+            msg = (self._L.havac_cuda_last_error(None) or b"").decode()
+            self._h = C.c_void_p()
+            self._raise(rc, msg)
+        self.kernelName = havacKernelName
+
+    # -- error mapping ---------------------------------------------------------------------
+    def _raise(self, rc: int, msg: Optional[str] = None):
+        if msg is None:
+            msg = (self._L.havac_cuda_last_error(self._h) or b"").decode()
+        if rc == E_LENGTH:
+            raise ValueError(msg)  # std::length_error
+        if rc == E_LOGIC:
+            raise LogicError(msg)
+        if rc == E_NOMEM:
+            raise MemoryError(msg)
+        if rc == E_OVERFLOW:
+            raise HitOverflowError(msg)
+        raise RuntimeError(f"[havac_cuda rc={rc}] {msg}")
+
+    def _ck(self, rc: int):
+        if rc != OK:
+            self._raise(rc)
+
+    # -- the reference client's methods ------------------------------------------------------
+    def writeSequence(self, compressedSequence) -> None:
+        a = np.ascontiguousarray(compressedSequence, dtype=np.uint8)
+        self._ck(self._L.havac_cuda_write_sequence(self._h, a.ctypes.data, a.nbytes))
+
+    def writePhmm(self, phmmAsFlattenedArray) -> None:
+        a = np.ascontiguousarray(phmmAsFlattenedArray, dtype=np.int8).reshape(-1)
+        self._ck(self._L.havac_cuda_write_phmm(self._h, a.ctypes.data, a.nbytes))
+
+    def invokeHavacSsvAsync(self) -> None:
+        self._ck(self._L.havac_cuda_invoke_async(self._h))
+
+    def getHwState(self) -> int:
+        st = C.c_int(0)
+        self._ck(self._L.havac_cuda_state(self._h, C.byref(st)))
+        return st.value
+
+    def waitForHavacSsvAsync(self, timeout_ms: int = 0) -> int:
+        st = C.c_int(0)
+        self._ck(self._L.havac_cuda_wait(self._h, timeout_ms, C.byref(st)))
+        return st.value
+
+    def abort(self) -> int:
+        st = C.c_int(0)
+        self._ck(self._L.havac_cuda_abort(self._h, C.byref(st)))
+        return st.value
+
+    def getNumHits(self) -> int:
+        n = C.c_uint64(0)
+        self._ck(self._L.havac_cuda_num_hits(self._h, C.byref(n)))
+        return n.value
+
+    def getHitList(self) -> np.ndarray:
+        n = self.getNumHits()
+        out = np.zeros(n, dtype=np.uint64)
+        got = C.c_uint64(0)
+        self._ck(self._L.havac_cuda_read_hits(self._h, out.ctypes.data, n, C.byref(got)))
+        return out[: got.value]
+
+    # -- harness helpers (no reference counterpart) ----------------------------------------------
+    def setSegmentRange(self, segBegin: int, segEnd: int = 0) -> None:
+        self._ck(self._L.havac_cuda_set_segment_range(self._h, segBegin, segEnd))
+
+    def setKernel(self, name: str) -> None:
+        self._ck(self._L.havac_cuda_set_kernel(self._h, name.encode()))
+
+    def deviceTimeMs(self) -> float:
+        ms = C.c_float(0)
+        self._ck(self._L.havac_cuda_device_time_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def deviceCount(self) -> int:
+        n = C.c_int(0)
+        self._ck(self._L.havac_cuda_device_count(self._h, C.byref(n)))
+        return n.value
+
+    def runStats(self):
+        cells, launches = C.c_uint64(0), C.c_uint32(0)
+        self._ck(self._L.havac_cuda_run_stats(self._h, C.byref(cells), C.byref(launches)))
+        return cells.value, launches.value
+
+    def close(self) -> None:
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.havac_cuda_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,502 @@
+// havac_cuda.cu -- implementation of the C-ABI device client declared in include/havac_cuda.h.
+// It stands where the reference's HavacHwClient talks to XRT (host/HavacHwClient.cpp): device
+// buffers, asynchronous launch, state/wait/abort, hit read-back. One client may drive several
+// GPUs of this process; the sequence axis is split on segment boundaries with a left halo of
+// (rows - 1) symbols per shard, which makes every shard's hits exact without any exchange
+// between devices (each diagonal is an independent chain).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/havac_cuda.h"
+#include "ssv_kernels.cuh"
+
+namespace {
+
+constexpr long long SEG = HAVAC_CUDA_SEGMENT_SYMBOLS;
+constexpr unsigned long long MAX_ROWS = 1ull << 24;  // phmmPos_t is 24 bits (device/HavacHls.hpp:19)
+constexpr long long HALO_RESIDENT = 1ll << 24;       // symbols kept left of a shard (>= MAX_ROWS - 1)
+
+thread_local std::string g_createError;
+
+enum KernelKind { KERNEL_AUTO = 0, KERNEL_F16X2 = 1, KERNEL_SCALAR = 2 };
+
+struct DeviceCtx {
+  int dev = 0;
+  int numSMs = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t evStart = nullptr, evStop = nullptr;
+  // sequence shard
+  uint32_t* dSeq = nullptr;
+  long long resBegin = 0, resEnd = 0;  // global columns resident in dSeq
+  long long colBegin = 0, colEnd = 0;  // global columns whose hits this device reports
+  // score table
+  int8_t* dTab8 = nullptr;
+  uint2* dTab16 = nullptr;
+  uint32_t rowsPadded = 0;
+  // outputs
+  unsigned long long* dHits = nullptr;
+  unsigned long long* dHitCount = nullptr;
+  unsigned int* dTileCounter = nullptr;
+  int* dStatus = nullptr;
+  // results of the last finished run
+  unsigned long long hitCount = 0;
+  int status = 0;
+};
+
+}  // namespace
+
+struct havac_cuda_client {
+  std::vector<DeviceCtx> devs;
+  std::string err;
+  unsigned long long hitCap = 16ull << 20;  // per device
+  uint64_t segBegin = 0, segEnd = 0;        // 0,0 = whole buffer
+  uint64_t seqSegments = 0;                 // segments in the buffer given to write_sequence
+  uint32_t nRows = 0;
+  bool launched = false, finished = false, aborted = false;
+  int finalState = HAVAC_CUDA_STATE_NEW;
+  int* hostAbort = nullptr;  // mapped, portable pinned int polled by the kernels
+  int kernel = KERNEL_AUTO;
+  uint32_t launches = 0;
+  float lastMs = 0.f;
+};
+
+namespace {
+
+#define CK(call)                                                                         \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) {                                                             \
+      c->err = std::string(#call) + ": " + cudaGetErrorString(e_);                       \
+      return e_ == cudaErrorMemoryAllocation ? HAVAC_CUDA_E_NOMEM : HAVAC_CUDA_E_RUNTIME; \
+    }                                                                                    \
+  } while (0)
+
+int fail(havac_cuda_client* c, int code, const std::string& msg) {
+  if (c) c->err = msg;
+  else g_createError = msg;
+  return code;
+}
+
+bool parse_spec(const char* spec, uint32_t deviceIndex, int nDev, std::vector<int>& out,
+                unsigned long long& hitCap, std::string& err) {
+  std::string s = spec ? spec : "";
+  std::string devPart = s;
+  size_t semi = s.find(';');
+  if (semi != std::string::npos) {
+    devPart = s.substr(0, semi);
+    std::string opt = s.substr(semi + 1);
+    if (opt.rfind("hitcap=", 0) == 0) hitCap = strtoull(opt.c_str() + 7, nullptr, 10);
+    if (hitCap == 0) { err = "hitcap must be positive"; return false; }
+  }
+  if (devPart.rfind("cuda:", 0) != 0) {  // an xclbin path or empty: single device
+    out.push_back((int)deviceIndex);
+  } else {
+    std::string list = devPart.substr(5);
+    if (list == "all") {
+      for (int i = 0; i < nDev; i++) out.push_back(i);
+    } else {
+      size_t pos = 0;
+      while (pos <= list.size()) {
+        size_t comma = list.find(',', pos);
+        std::string tok = list.substr(pos, comma == std::string::npos ? std::string::npos : comma - pos);
+        if (tok.empty() || tok.find_first_not_of("0123456789") != std::string::npos) {
+          err = "bad device list '" + list + "'";
+          return false;
+        }
+        out.push_back(atoi(tok.c_str()));
+        if (comma == std::string::npos) break;
+        pos = comma + 1;
+      }
+    }
+  }
+  for (int d : out)
+    if (d < 0 || d >= nDev) {
+      err = "CUDA device " + std::to_string(d) + " not present (" + std::to_string(nDev) + " visible)";
+      return false;
+    }
+  return !out.empty();
+}
+
+void free_sequence(DeviceCtx& d) {
+  if (d.dSeq) { cudaSetDevice(d.dev); cudaFree(d.dSeq); d.dSeq = nullptr; }
+}
+void free_table(DeviceCtx& d) {
+  cudaSetDevice(d.dev);
+  if (d.dTab8) { cudaFree(d.dTab8); d.dTab8 = nullptr; }
+  if (d.dTab16) { cudaFree(d.dTab16); d.dTab16 = nullptr; }
+}
+
+// Pull the per-device results after the stop events have fired; decides the final state.
+int collect(havac_cuda_client* c) {
+  if (c->finished) return HAVAC_CUDA_OK;
+  float worst = 0.f;
+  bool overflow = false, aborted = false;
+  for (DeviceCtx& d : c->devs) {
+    CK(cudaSetDevice(d.dev));
+    CK(cudaEventSynchronize(d.evStop));
+    CK(cudaMemcpy(&d.hitCount, d.dHitCount, sizeof d.hitCount, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(&d.status, d.dStatus, sizeof d.status, cudaMemcpyDeviceToHost));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, d.evStart, d.evStop));
+    worst = std::max(worst, ms);
+    overflow |= (d.status & SSV_STATUS_OVERFLOW) != 0 || d.hitCount > c->hitCap;
+    aborted |= (d.status & SSV_STATUS_ABORTED) != 0;
+  }
+  c->lastMs = worst;
+  c->finished = true;
+  c->aborted = aborted;
+  if (aborted) c->finalState = HAVAC_CUDA_STATE_ABORT;
+  else if (overflow) {
+    c->finalState = HAVAC_CUDA_STATE_ERROR;
+    c->err = "device hit buffer overflowed (capacity " + std::to_string(c->hitCap) + " hits per device)";
+  } else c->finalState = HAVAC_CUDA_STATE_COMPLETED;
+  return HAVAC_CUDA_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int havac_cuda_create(const char* deviceSpec, uint32_t deviceIndex, havac_cuda_client** out) {
+  if (!out) return fail(nullptr, HAVAC_CUDA_E_INVALID, "null output handle");
+  *out = nullptr;
+  int nDev = 0;
+  cudaError_t e = cudaGetDeviceCount(&nDev);
+  if (e != cudaSuccess || nDev == 0)
+    return fail(nullptr, HAVAC_CUDA_E_NODEVICE,
+                std::string("no CUDA device available: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "count is 0"));
+  std::vector<int> ids;
+  unsigned long long hitCap = 16ull << 20;
+  std::string perr;
+  if (!parse_spec(deviceSpec, deviceIndex, nDev, ids, hitCap, perr)) return fail(nullptr, HAVAC_CUDA_E_NODEVICE, perr);
+
+  havac_cuda_client* c = new (std::nothrow) havac_cuda_client();
+  if (!c) return fail(nullptr, HAVAC_CUDA_E_NOMEM, "out of host memory");
+  c->hitCap = hitCap;
+  auto bail = [&](int code) { g_createError = c->err; havac_cuda_destroy(c); return code; };
+  {
+    cudaError_t ee = cudaHostAlloc((void**)&c->hostAbort, sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable);
+    if (ee != cudaSuccess) { c->err = std::string("cudaHostAlloc: ") + cudaGetErrorString(ee); return bail(HAVAC_CUDA_E_NOMEM); }
+    *c->hostAbort = 0;
+  }
+  for (int id : ids) {
+    DeviceCtx d;
+    d.dev = id;
+    c->devs.push_back(d);
+  }
+  for (DeviceCtx& d : c->devs) {
+    auto ck = [&](cudaError_t ee, const char* what) {
+      if (ee == cudaSuccess) return true;
+      c->err = std::string(what) + ": " + cudaGetErrorString(ee);
+      return false;
+    };
+    cudaDeviceProp prop;
+    if (!ck(cudaSetDevice(d.dev), "cudaSetDevice") || !ck(cudaGetDeviceProperties(&prop, d.dev), "cudaGetDeviceProperties"))
+      return bail(HAVAC_CUDA_E_RUNTIME);
+    if (prop.major < 10) {
+      c->err = "device " + std::to_string(d.dev) + " (" + prop.name + ") is sm_" + std::to_string(prop.major) +
+               std::to_string(prop.minor) + "; this library carries sm_100a code only";
+      return bail(HAVAC_CUDA_E_NODEVICE);
+    }
+    d.numSMs = prop.multiProcessorCount;
+    if (!ck(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
+        !ck(cudaEventCreate(&d.evStart), "cudaEventCreate") || !ck(cudaEventCreate(&d.evStop), "cudaEventCreate"))
+      return bail(HAVAC_CUDA_E_RUNTIME);
+    // the hit buffers are allocated once, like HavacHwClient::allocateOutputBuffers (HavacHwClient.cpp:73-76)
+    if (!ck(cudaMalloc(&d.dHits, c->hitCap * sizeof(unsigned long long)), "cudaMalloc(hits)") ||
+        !ck(cudaMalloc(&d.dHitCount, sizeof(unsigned long long)), "cudaMalloc") ||
+        !ck(cudaMalloc(&d.dTileCounter, sizeof(unsigned int)), "cudaMalloc") ||
+        !ck(cudaMalloc(&d.dStatus, sizeof(int)), "cudaMalloc"))
+      return bail(HAVAC_CUDA_E_NOMEM);
+  }
+  *out = c;
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_destroy(havac_cuda_client* c) {
+  if (!c) return HAVAC_CUDA_E_INVALID;
+  if (c->hostAbort) *c->hostAbort = 1;  // let a still-running kernel drain quickly
+  for (DeviceCtx& d : c->devs) {
+    cudaSetDevice(d.dev);
+    if (d.stream) cudaStreamSynchronize(d.stream);
+    free_sequence(d);
+    free_table(d);
+    if (d.dHits) cudaFree(d.dHits);
+    if (d.dHitCount) cudaFree(d.dHitCount);
+    if (d.dTileCounter) cudaFree(d.dTileCounter);
+    if (d.dStatus) cudaFree(d.dStatus);
+    if (d.evStart) cudaEventDestroy(d.evStart);
+    if (d.evStop) cudaEventDestroy(d.evStop);
+    if (d.stream) cudaStreamDestroy(d.stream);
+  }
+  if (c->hostAbort) cudaFreeHost(c->hostAbort);
+  delete c;
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_set_segment_range(havac_cuda_client* c, uint64_t segBegin, uint64_t segEnd) {
+  if (!c) return HAVAC_CUDA_E_INVALID;
+  if (segEnd != 0 && segEnd <= segBegin) return fail(c, HAVAC_CUDA_E_LENGTH, "empty segment range");
+  c->segBegin = segBegin;
+  c->segEnd = segEnd;
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_write_sequence(havac_cuda_client* c, const uint8_t* packed, uint64_t nBytes) {
+  if (!c || (!packed && nBytes)) return HAVAC_CUDA_E_INVALID;
+  // host/HavacHwClient.cpp:81-97: whole segments only, and strictly less than 4 GiB packed
+  uint64_t nSymbols = nBytes * 4;
+  if (nSymbols % SEG != 0)
+    return fail(c, HAVAC_CUDA_E_LENGTH, "sequence length must be a multiple of the sequence segment length " +
+                                            std::to_string(SEG) + " but sequence of length " + std::to_string(nSymbols) + " was not");
+  if (nBytes >= 4ull * 1024 * 1024 * 1024)
+    return fail(c, HAVAC_CUDA_E_LENGTH, "compressed sequence size must be less than 4GiB. length requested: " +
+                                            std::to_string(nBytes) + " bytes.");
+  if (c->launched && !c->finished) return fail(c, HAVAC_CUDA_E_LOGIC, "a run is in flight");
+  c->seqSegments = nSymbols / SEG;
+  uint64_t sb = c->segBegin, se = c->segEnd ? c->segEnd : c->seqSegments;
+  if (se > c->seqSegments) se = c->seqSegments;
+  if (sb > se) sb = se;
+  const uint64_t nSeg = se - sb;
+  const size_t nd = c->devs.size();
+  for (size_t i = 0; i < nd; i++) {
+    DeviceCtx& d = c->devs[i];
+    free_sequence(d);
+    d.colBegin = (long long)((sb + nSeg * i / nd) * SEG);
+    d.colEnd = (long long)((sb + nSeg * (i + 1) / nd) * SEG);
+    d.resBegin = std::max(0ll, d.colBegin - HALO_RESIDENT) & ~63ll;
+    d.resEnd = d.colEnd;
+    if (d.colEnd <= d.colBegin) { d.resBegin = d.resEnd = d.colBegin; continue; }
+    size_t bytes = (size_t)(d.resEnd - d.resBegin) / 4;
+    CK(cudaSetDevice(d.dev));
+    CK(cudaMalloc(&d.dSeq, bytes));
+    CK(cudaMemcpyAsync(d.dSeq, packed + d.resBegin / 4, bytes, cudaMemcpyHostToDevice, d.stream));
+  }
+  for (DeviceCtx& d : c->devs) {  // the reference's bo.sync is blocking too (HavacHwClient.cpp:104)
+    CK(cudaSetDevice(d.dev));
+    CK(cudaStreamSynchronize(d.stream));
+  }
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_write_phmm(havac_cuda_client* c, const int8_t* flat, uint64_t nBytes) {
+  if (!c || (!flat && nBytes)) return HAVAC_CUDA_E_INVALID;
+  // host/HavacHwClient.cpp:112-125
+  if (nBytes % 4 != 0)
+    return fail(c, HAVAC_CUDA_E_LENGTH, "phmm of length " + std::to_string(nBytes) +
+                                            " was given, but was not divisible by 4. only nucleotide phmms with 4 scores/position is supported.");
+  if (nBytes >= 1024ull * 1024 * 1024)
+    return fail(c, HAVAC_CUDA_E_LENGTH, "model length must be less than 1GiB. length requested: " + std::to_string(nBytes) + " bytes.");
+  if (nBytes / 4 > MAX_ROWS)
+    return fail(c, HAVAC_CUDA_E_LENGTH, "more than 2^24 model positions: the hit word holds the row in 24 bits");
+  if (c->launched && !c->finished) return fail(c, HAVAC_CUDA_E_LOGIC, "a run is in flight");
+  c->nRows = (uint32_t)(nBytes / 4);
+  for (DeviceCtx& d : c->devs) {
+    free_table(d);
+    if (c->nRows == 0) continue;
+    d.rowsPadded = (c->nRows + SSV_ROW_CHUNK - 1) / SSV_ROW_CHUNK * SSV_ROW_CHUNK;
+    CK(cudaSetDevice(d.dev));
+    CK(cudaMalloc(&d.dTab8, nBytes));
+    CK(cudaMalloc(&d.dTab16, (size_t)d.rowsPadded * sizeof(uint2)));
+    CK(cudaMemcpyAsync(d.dTab8, flat, nBytes, cudaMemcpyHostToDevice, d.stream));
+    ssv_launch_table_prep(d.dTab8, c->nRows, d.dTab16, d.rowsPadded, d.stream);
+    CK(cudaGetLastError());
+  }
+  for (DeviceCtx& d : c->devs) {
+    CK(cudaSetDevice(d.dev));
+    CK(cudaStreamSynchronize(d.stream));
+  }
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_invoke_async(havac_cuda_client* c) {
+  if (!c) return HAVAC_CUDA_E_INVALID;
+  // host/HavacHwClient.cpp:142-147
+  if (c->seqSegments == 0) return fail(c, HAVAC_CUDA_E_LENGTH, "sequence length in segments cannot be 0, but 0 was given to the client.");
+  if (c->nRows == 0) return fail(c, HAVAC_CUDA_E_LENGTH, "phmm length in vectors cannot be 0, but 0 was given to the client.");
+  if (c->launched && !c->finished) return fail(c, HAVAC_CUDA_E_LOGIC, "a run is already in flight");
+  *c->hostAbort = 0;
+  c->launches = 0;
+  for (DeviceCtx& d : c->devs) {
+    CK(cudaSetDevice(d.dev));
+    CK(cudaMemsetAsync(d.dHitCount, 0, sizeof(unsigned long long), d.stream));
+    CK(cudaMemsetAsync(d.dTileCounter, 0, sizeof(unsigned int), d.stream));
+    CK(cudaMemsetAsync(d.dStatus, 0, sizeof(int), d.stream));
+    CK(cudaEventRecord(d.evStart, d.stream));
+    if (d.colEnd > d.colBegin) {
+      SsvParams p{};
+      const long long P = c->nRows;
+      long long loadBegin = std::max(d.resBegin, (d.colBegin - (P - 1)) & ~63ll);
+      if (loadBegin < 0) loadBegin = 0;
+      p.seqPacked = d.dSeq + (loadBegin - d.resBegin) / 16;
+      p.nLoad = d.resEnd - loadBegin;
+      p.loadBegin = loadBegin;
+      p.colBegin = d.colBegin;
+      p.colEnd = d.colEnd;
+      p.tab16 = d.dTab16;
+      p.tab8 = d.dTab8;
+      p.nRows = c->nRows;
+      p.rowsPadded = d.rowsPadded;
+      long long dLo = d.colBegin - loadBegin - (P - 1);  // first diagonal that can reach a reported column
+      p.diagBegin = dLo >= 0 ? (dLo & ~63ll) : -((-dLo + 63) & ~63ll);
+      p.nTiles = (uint32_t)((p.nLoad - p.diagBegin + SSV_TILE_DIAGS - 1) / SSV_TILE_DIAGS);
+      p.hits = d.dHits;
+      p.hitCap = c->hitCap;
+      p.hitCount = d.dHitCount;
+      p.tileCounter = d.dTileCounter;
+      int* devAbort = nullptr;
+      CK(cudaHostGetDevicePointer((void**)&devAbort, c->hostAbort, 0));
+      p.abortFlag = devAbort;
+      p.status = d.dStatus;
+      if (c->kernel == KERNEL_SCALAR) ssv_launch_scalar(p, d.stream);
+      else ssv_launch_f16x2(p, d.numSMs, d.stream);
+      CK(cudaGetLastError());
+      c->launches++;
+    }
+    CK(cudaEventRecord(d.evStop, d.stream));
+  }
+  c->launched = true;
+  c->finished = false;
+  c->aborted = false;
+  c->finalState = HAVAC_CUDA_STATE_QUEUED;
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_state(havac_cuda_client* c, int* state) {
+  if (!c || !state) return HAVAC_CUDA_E_INVALID;
+  if (!c->launched)  // host/HavacHwClient.cpp:163-170
+    return fail(c, HAVAC_CUDA_E_LOGIC, "run object was not initialized. run function invokeHavacSsvAsync to initialize this object.");
+  if (c->finished) { *state = c->finalState; return HAVAC_CUDA_OK; }
+  bool allDone = true, anyStarted = false;
+  for (DeviceCtx& d : c->devs) {
+    CK(cudaSetDevice(d.dev));
+    cudaError_t e = cudaEventQuery(d.evStop);
+    if (e == cudaErrorNotReady) allDone = false;
+    else if (e != cudaSuccess) { c->err = cudaGetErrorString(e); *state = HAVAC_CUDA_STATE_ERROR; return HAVAC_CUDA_E_RUNTIME; }
+    if (cudaEventQuery(d.evStart) == cudaSuccess) anyStarted = true;
+  }
+  if (allDone) {
+    int rc = collect(c);
+    if (rc) return rc;
+    *state = c->finalState;
+  } else {
+    *state = anyStarted ? HAVAC_CUDA_STATE_RUNNING : HAVAC_CUDA_STATE_QUEUED;
+  }
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_wait(havac_cuda_client* c, uint64_t timeoutMs, int* state) {
+  if (!c) return HAVAC_CUDA_E_INVALID;
+  if (!c->launched) return fail(c, HAVAC_CUDA_E_LOGIC, "nothing was launched");
+  int st = 0;
+  if (timeoutMs == 0) {
+    int rc = collect(c);  // blocks on the stop events
+    if (rc) return rc;
+    st = c->finalState;
+  } else {
+    auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(timeoutMs);
+    while (true) {
+      int rc = havac_cuda_state(c, &st);
+      if (rc) return rc;
+      if (c->finished) break;
+      if (std::chrono::steady_clock::now() >= deadline) { st = HAVAC_CUDA_STATE_TIMEOUT; break; }
+      std::this_thread::sleep_for(std::chrono::microseconds(200));
+    }
+  }
+  if (state) *state = st;
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_abort(havac_cuda_client* c, int* state) {
+  if (!c) return HAVAC_CUDA_E_INVALID;
+  if (!c->launched) return fail(c, HAVAC_CUDA_E_LOGIC, "nothing was launched");
+  if (!c->finished) {
+    *c->hostAbort = 1;
+    int rc = collect(c);
+    if (rc) return rc;
+  }
+  if (state) *state = c->finalState;
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_num_hits(havac_cuda_client* c, uint64_t* n) {
+  if (!c || !n) return HAVAC_CUDA_E_INVALID;
+  if (!c->launched) return fail(c, HAVAC_CUDA_E_LOGIC, "no run to read hits from");
+  int rc = collect(c);
+  if (rc) return rc;
+  if (c->finalState == HAVAC_CUDA_STATE_ERROR) return HAVAC_CUDA_E_OVERFLOW;
+  uint64_t total = 0;
+  for (DeviceCtx& d : c->devs) total += d.hitCount;
+  *n = total;
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_read_hits(havac_cuda_client* c, uint64_t* out, uint64_t cap, uint64_t* n) {
+  uint64_t total = 0;
+  int rc = havac_cuda_num_hits(c, &total);
+  if (rc) return rc;
+  if (n) *n = total;
+  if (total == 0) return HAVAC_CUDA_OK;
+  if (!out || cap < total) return fail(c, HAVAC_CUDA_E_LENGTH, "hit buffer too small: " + std::to_string(total) + " hits");
+  uint64_t off = 0;
+  for (DeviceCtx& d : c->devs) {
+    if (!d.hitCount) continue;
+    CK(cudaSetDevice(d.dev));
+    CK(cudaMemcpy(out + off, d.dHits, d.hitCount * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    off += d.hitCount;
+  }
+  // the FPGA emits hits by (segment, row, cell) ascending (device/HavacHls.cpp:131-162 outer loop
+  // over segments, inner over rows, sieve in cell order); reproduce that order.
+  auto key = [](uint64_t h) {
+    uint64_t cell = h & 0x3fffu, seg = (h >> 14) & 0x3ffffffu, row = h >> 40;
+    return (seg << 38) | (row << 14) | cell;
+  };
+  std::sort(out, out + total, [&](uint64_t a, uint64_t b) { return key(a) < key(b); });
+  return HAVAC_CUDA_OK;
+}
+
+const char* havac_cuda_last_error(havac_cuda_client* c) { return c ? c->err.c_str() : g_createError.c_str(); }
+
+int havac_cuda_device_time_ms(havac_cuda_client* c, float* ms) {
+  if (!c || !ms) return HAVAC_CUDA_E_INVALID;
+  if (!c->launched) return fail(c, HAVAC_CUDA_E_LOGIC, "nothing was launched");
+  int rc = collect(c);
+  if (rc) return rc;
+  *ms = c->lastMs;
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_device_count(havac_cuda_client* c, int* n) {
+  if (!c || !n) return HAVAC_CUDA_E_INVALID;
+  *n = (int)c->devs.size();
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_run_stats(havac_cuda_client* c, uint64_t* cells, uint32_t* launches) {
+  if (!c) return HAVAC_CUDA_E_INVALID;
+  uint64_t cols = 0;
+  for (DeviceCtx& d : c->devs) cols += (uint64_t)(d.colEnd - d.colBegin);
+  if (cells) *cells = cols * c->nRows;
+  if (launches) *launches = c->launches;
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_set_kernel(havac_cuda_client* c, const char* name) {
+  if (!c || !name) return HAVAC_CUDA_E_INVALID;
+  std::string s = name;
+  if (s == "auto") c->kernel = KERNEL_AUTO;
+  else if (s == "f16x2") c->kernel = KERNEL_F16X2;
+  else if (s == "scalar") c->kernel = KERNEL_SCALAR;
+  else return fail(c, HAVAC_CUDA_E_INVALID, "unknown kernel '" + s + "'");
+  return HAVAC_CUDA_OK;
+}
+
+}  // extern "C"

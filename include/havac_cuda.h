@@ -1,0 +1,118 @@
+/*
+ * havac_cuda.h -- the drop-in boundary: a C-ABI device client for the HAVAC SSV
+ * filter on NVIDIA B200 (sm_100a).
+ *
+ * It serves exactly the calls the reference's `class HavacHwClient` makes into
+ * XRT (host/HavacHwClient.hpp:21-115); the `Havac` driver above it keeps its
+ * public API unchanged (host/Havac.hpp:42-107). Plain pointers and sizes only:
+ * no C++, CUDA or torch types cross this boundary. Every function returns 0 on
+ * success or a negative HAVAC_CUDA_E_* code and never throws.
+ *
+ * Wire formats (bit-identical to the FPGA design):
+ *   sequence : 2 bits/symbol, symbol k in byte k/4 at bit (k%4)*2, a whole number
+ *              of 12288-symbol segments (device/PublicDefines.h:18-22,
+ *              host/sequence/SequencePreprocessor.cpp:37-59).
+ *   table    : int8 [row][A,C,G,T], models concatenated with no separator, hit
+ *              threshold projected to exactly 256 (host/phmm/PhmmPreprocessor.cpp:9-31).
+ *   hit      : u64 = cell[13:0] | segment[39:14] | row[63:40]
+ *              (device/HitReporting.cpp:421-430).
+ */
+#ifndef HAVAC_CUDA_H
+#define HAVAC_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HAVAC_CUDA_SEGMENT_SYMBOLS 12288u
+
+/* error codes */
+#define HAVAC_CUDA_OK 0
+#define HAVAC_CUDA_E_INVALID (-1)   /* bad argument / null handle                       */
+#define HAVAC_CUDA_E_LENGTH (-2)    /* size contract broken  -> std::length_error        */
+#define HAVAC_CUDA_E_LOGIC (-3)     /* call out of order     -> std::logic_error         */
+#define HAVAC_CUDA_E_RUNTIME (-4)   /* CUDA failure          -> std::runtime_error       */
+#define HAVAC_CUDA_E_NOMEM (-5)     /* allocation failure    -> std::bad_alloc           */
+#define HAVAC_CUDA_E_NODEVICE (-6)  /* no usable CUDA device -> std::runtime_error       */
+#define HAVAC_CUDA_E_OVERFLOW (-7)  /* device hit buffer overflowed (the FPGA design does
+                                       not check this: device/HitReporting.cpp:412)     */
+
+/* Command states: numerically identical to XRT's ert_cmd_state, which
+ * HavacHwClient::getHwState returns and host/Havac.hpp:16-26 mirrors. */
+#define HAVAC_CUDA_STATE_NEW 1
+#define HAVAC_CUDA_STATE_QUEUED 2
+#define HAVAC_CUDA_STATE_RUNNING 3
+#define HAVAC_CUDA_STATE_COMPLETED 4
+#define HAVAC_CUDA_STATE_ERROR 5
+#define HAVAC_CUDA_STATE_ABORT 6
+#define HAVAC_CUDA_STATE_SUBMITTED 7
+#define HAVAC_CUDA_STATE_TIMEOUT 8
+#define HAVAC_CUDA_STATE_NORESPONSE 9
+
+typedef struct havac_cuda_client havac_cuda_client; /* opaque, one per Havac object */
+
+/* Replaces HavacHwClient::HavacHwClient (host/HavacHwClient.cpp:24-31: open device,
+ * load xclbin, allocate the hit buffers). `deviceSpec` takes the place of the xclbin
+ * path: NULL, "" or anything not starting with "cuda:" selects the single GPU
+ * `deviceIndex`; "cuda:all" or "cuda:0,1,2" shards the sequence over those GPUs of
+ * this process. Optional ";hitcap=<n>" sets the per-device hit capacity. */
+int havac_cuda_create(const char* deviceSpec, uint32_t deviceIndex, havac_cuda_client** out);
+int havac_cuda_destroy(havac_cuda_client* c);
+
+/* Replaces HavacHwClient::writeSequence (host/HavacHwClient.cpp:78-110).
+ * nBytes*4 must be a multiple of 12288 and nBytes < 4 GiB, else E_LENGTH. The data
+ * is copied; the caller keeps ownership of `packed2bit`. */
+int havac_cuda_write_sequence(havac_cuda_client* c, const uint8_t* packed2bit, uint64_t nBytes);
+
+/* Replaces HavacHwClient::writePhmm (host/HavacHwClient.cpp:111-138).
+ * nBytes must be a multiple of 4 and < 1 GiB, else E_LENGTH. */
+int havac_cuda_write_phmm(havac_cuda_client* c, const int8_t* flatScores, uint64_t nBytes);
+
+/* Restrict this client to the sequence segments [segBegin, segEnd) of the buffer
+ * given to write_sequence (it keeps a left halo of rows-1 symbols so the hits in
+ * that range are exact). Used by one-process-per-GPU launchers to shard the
+ * database; call before write_sequence. segEnd = 0 means "to the end". No
+ * reference counterpart (the FPGA is a single card). */
+int havac_cuda_set_segment_range(havac_cuda_client* c, uint64_t segBegin, uint64_t segEnd);
+
+/* Replaces HavacHwClient::invokeHavacSsvAsync (host/HavacHwClient.cpp:141-151):
+ * E_LENGTH when either input has zero length; returns as soon as the work is queued. */
+int havac_cuda_invoke_async(havac_cuda_client* c);
+
+/* Replaces HavacHwClient::getHwState (host/HavacHwClient.cpp:163-170): E_LOGIC when
+ * nothing was ever launched. */
+int havac_cuda_state(havac_cuda_client* c, int* state);
+
+/* Replaces HavacHwClient::waitForHavacSsvAsync (host/HavacHwClient.cpp:153-157):
+ * timeoutMs = 0 waits forever; otherwise *state is HAVAC_CUDA_STATE_TIMEOUT when the
+ * run is still going after timeoutMs. */
+int havac_cuda_wait(havac_cuda_client* c, uint64_t timeoutMs, int* state);
+
+/* Replaces HavacHwClient::abort (host/HavacHwClient.cpp:159-161): raises a flag the
+ * persistent kernel polls between tiles, waits for it to drain, reports ABORT. */
+int havac_cuda_abort(havac_cuda_client* c, int* state);
+
+/* Replace HavacHwClient::getNumHits / getHitList (host/HavacHwClient.cpp:172-203).
+ * Hits come back in the FPGA's emission order (segment, row, cell ascending).
+ * E_LOGIC before a completed run, E_OVERFLOW when the device buffer overflowed. */
+int havac_cuda_num_hits(havac_cuda_client* c, uint64_t* n);
+int havac_cuda_read_hits(havac_cuda_client* c, uint64_t* out, uint64_t cap, uint64_t* n);
+
+/* Harness helpers (no reference counterpart). */
+const char* havac_cuda_last_error(havac_cuda_client* c); /* c may be NULL: last create error */
+int havac_cuda_device_time_ms(havac_cuda_client* c, float* ms); /* CUDA-event time of the last
+                                                                   run, max over devices       */
+int havac_cuda_device_count(havac_cuda_client* c, int* n);
+/* Per-run facts for roofline accounting: cells = real cells computed (rows x columns
+ * of this client's range, halo and padding excluded); launches = kernels launched. */
+int havac_cuda_run_stats(havac_cuda_client* c, uint64_t* cells, uint32_t* launches);
+/* Select a kernel variant by name ("auto" | "f16x2" | "scalar"); for tests that
+ * cross-check the fast path against the plain one. */
+int havac_cuda_set_kernel(havac_cuda_client* c, const char* name);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HAVAC_CUDA_H */

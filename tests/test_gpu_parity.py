@@ -1,0 +1,149 @@
+"""GPU parity: the CUDA path, called through the C-ABI (include/havac_cuda.h), against the
+CPU oracle (oracle/soft_ssv.c, a restatement of test/softSsv/SoftSsv.cpp:15-67) on the same
+packed sequence buffer and the same int8 table. Integer work: the bar is bit-exact equality
+of the raw u64 hit sets (the reference's own comparators check set membership only,
+device/test/softwareTestbench.cpp:224-306)."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from havac_b200 import synth
+from havac_b200.client import HavacHwClient, STATE_COMPLETED
+
+pytestmark = pytest.mark.gpu
+
+
+def consensus_table(seed, n_rows, hi=(14, 22), lo=(-32, -9)):
+    g = synth.rng(seed, 77)
+    t = g.integers(lo[0], lo[1] + 1, size=(n_rows, 4)).astype(np.int8)
+    cons = g.integers(0, 4, size=n_rows)
+    t[np.arange(n_rows), cons] = g.integers(hi[0], hi[1] + 1, size=n_rows)
+    return t, cons.astype(np.uint8)
+
+
+def planted_sequence(seed, n, cons, copies, sub=0.1):
+    g = synth.rng(seed, 78)
+    sym = synth.random_symbols(seed, n)
+    L = len(cons)
+    for _ in range(copies):
+        a = int(g.integers(0, L - 40)) if L > 80 else 0
+        b = int(g.integers(a + 40, L + 1)) if L > 80 else L
+        frag = cons[a:b].copy()
+        mut = g.random(len(frag)) < sub
+        frag[mut] = g.integers(0, 4, size=int(mut.sum()))
+        if len(frag) >= n:
+            continue
+        at = int(g.integers(0, n - len(frag)))
+        sym[at:at + len(frag)] = frag
+    return sym
+
+
+def gpu_hits(packed, table, kernel="auto", seg_range=None, spec=""):
+    c = HavacHwClient(spec)
+    try:
+        c.setKernel(kernel)
+        if seg_range:
+            c.setSegmentRange(*seg_range)
+        c.writeSequence(packed)
+        c.writePhmm(table)
+        c.invokeHavacSsvAsync()
+        assert c.waitForHavacSsvAsync() == STATE_COMPLETED
+        return c.getHitList()
+    finally:
+        c.close()
+
+
+def oracle_hits(packed, table):
+    sym = synth.unpack_2bit(packed)
+    pos, row = O.soft_ssv(sym, table)
+    return np.sort(O.encode_hits(pos, row))
+
+
+def check(packed, table, kernels=("f16x2", "scalar"), min_hits=1):
+    want = oracle_hits(packed, table)
+    assert len(want) >= min_hits, "test input produced too few oracle hits to be meaningful"
+    for k in kernels:
+        got = np.sort(gpu_hits(packed, table, k))
+        assert len(got) == len(want), f"{k}: {len(got)} hits vs oracle {len(want)}"
+        assert np.array_equal(got, want), f"{k}: hit sets differ"
+    return want
+
+
+def test_small_two_models():
+    t, cons = consensus_table(1, 257)
+    sym = planted_sequence(1, 100_000, cons, 12)
+    check(synth.pack_2bit(sym), t, min_hits=3)
+
+
+def test_rows_exceed_columns_left_edge():
+    """P_total > N: almost every diagonal starts on the left edge (column 0)."""
+    t, cons = consensus_table(2, 20_000)
+    sym = planted_sequence(2, 12_288, cons, 30)
+    check(synth.pack_2bit(sym), t, min_hits=3)
+
+
+def test_hit_dense_resets():
+    """Positive-drift table: every diagonal hits over and over, exercising reset-after-hit."""
+    g = synth.rng(3, 1)
+    t = g.integers(-20, 60, size=(300, 4)).astype(np.int8)
+    sym = synth.random_symbols(3, 30_000)
+    want = check(synth.pack_2bit(sym), t, min_hits=10_000)
+    assert len(want) > 10_000
+
+
+def test_extreme_scores():
+    g = synth.rng(4, 1)
+    t = g.choice(np.array([-128, -127, -1, 0, 1, 126, 127], dtype=np.int8), size=(500, 4))
+    sym = synth.random_symbols(4, 40_000)
+    check(synth.pack_2bit(sym), t, min_hits=100)
+
+
+def test_exact_255_is_not_a_hit():
+    """Score reaches exactly 255 (no hit) and exactly 256 (hit)."""
+    t = np.full((600, 4), -128, dtype=np.int8)
+    t[:, 0] = 51       # 5 x 51 = 255
+    t[5::7, 0] = -128  # two rows of -128 bring any score back to 0 ...
+    t[6::7, 0] = -128
+    t2 = t.copy()
+    t2[4::7, 0] = 52   # ... or 4 x 51 + 52 = 256 on the fifth
+    sym = np.zeros(12_288, dtype=np.uint8)
+    packed = synth.pack_2bit(sym)
+    assert len(oracle_hits(packed, t)) == 0
+    for k in ("f16x2", "scalar"):
+        assert len(gpu_hits(packed, t, k)) == 0
+    check(packed, t2, min_hits=1000)
+
+
+def test_config1_1mbp_x_200():
+    """BASELINE.json configs[0]: 1 Mbp x one 200-row model, homologs planted."""
+    t, cons = consensus_table(5, 200)
+    sym = planted_sequence(5, 1_000_000, cons, 40, sub=0.12)
+    check(synth.pack_2bit(sym), t, kernels=("f16x2",), min_hits=5)
+
+
+def test_long_model_crosses_many_chunks():
+    t, cons = consensus_table(6, 5_000)
+    sym = planted_sequence(6, 150_000, cons, 25)
+    check(synth.pack_2bit(sym), t, kernels=("f16x2",), min_hits=5)
+
+
+def test_segment_ranges_union_equals_whole():
+    """Sharding contract: hits of [a,b) segment ranges, each computed with its own
+    left halo, partition the hits of the whole run exactly."""
+    t, cons = consensus_table(7, 3_000)
+    sym = planted_sequence(7, 20 * 12_288, cons, 60)
+    packed = synth.pack_2bit(sym)
+    whole = np.sort(gpu_hits(packed, t))
+    assert len(whole) >= 5
+    parts = [gpu_hits(packed, t, seg_range=r) for r in ((0, 7), (7, 8), (8, 20))]
+    assert np.array_equal(np.sort(np.concatenate(parts)), whole)
+    assert np.array_equal(whole, oracle_hits(packed, t))
+
+
+def test_hit_order_matches_fpga_emission_order():
+    t, cons = consensus_table(8, 400)
+    sym = planted_sequence(8, 60_000, cons, 30)
+    hits = gpu_hits(synth.pack_2bit(sym), t)
+    cell, seg, row = hits & np.uint64(0x3fff), (hits >> np.uint64(14)) & np.uint64(0x3ffffff), hits >> np.uint64(40)
+    key = (seg << np.uint64(38)) | (row << np.uint64(14)) | cell
+    assert len(hits) > 1 and np.all(np.diff(key.astype(np.int64)) > 0)

@@ -1,0 +1,24 @@
+"""Quick device-timed throughput probe (development aid; bench.py is the contract)."""
+import os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+from havac_b200 import synth
+from havac_b200.client import HavacHwClient
+
+def main():
+    n = int(float(sys.argv[1])) if len(sys.argv) > 1 else 100_000_000
+    rows = int(float(sys.argv[2])) if len(sys.argv) > 2 else 35_000
+    reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
+    g = synth.rng(99, 1)
+    t = g.integers(-32, -8, size=(rows, 4)).astype(np.int8)
+    t[np.arange(rows), g.integers(0, 4, size=rows)] = g.integers(14, 23, size=rows)
+    packed = synth.random_packed(99, n)
+    c = HavacHwClient("")
+    c.writeSequence(packed); c.writePhmm(t)
+    for i in range(reps):
+        t0 = time.time(); c.invokeHavacSsvAsync(); st = c.waitForHavacSsvAsync(); wall = time.time() - t0
+        ms = c.deviceTimeMs()
+        print(f"run {i}: state={st} hits={c.getNumHits()} device={ms:.2f} ms wall={wall*1e3:.1f} ms  GCUPS={n*rows/ms/1e6:.1f}", flush=True)
+
+if __name__ == "__main__":
+    main()
