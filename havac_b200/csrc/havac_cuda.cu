@@ -46,6 +46,8 @@ struct DeviceCtx {
   unsigned long long* dHitCount = nullptr;
   unsigned int* dTileCounter = nullptr;
   int* dStatus = nullptr;
+  int* dAbort = nullptr;          // device-resident abort flag the kernels poll (L2 hit, no PCIe)
+  cudaStream_t ctlStream = nullptr;  // carries the abort write while the run stream is busy
   // results of the last finished run
   unsigned long long hitCount = 0;
   int status = 0;
@@ -62,7 +64,7 @@ struct havac_cuda_client {
   uint32_t nRows = 0;
   bool launched = false, finished = false, aborted = false;
   int finalState = HAVAC_CUDA_STATE_NEW;
-  int* hostAbort = nullptr;  // mapped, portable pinned int polled by the kernels
+  int* hostOne = nullptr;    // pinned source word for the asynchronous abort write
   int kernel = KERNEL_AUTO;
   uint32_t launches = 0;
   float lastMs = 0.f;
@@ -183,9 +185,9 @@ int havac_cuda_create(const char* deviceSpec, uint32_t deviceIndex, havac_cuda_c
   c->hitCap = hitCap;
   auto bail = [&](int code) { g_createError = c->err; havac_cuda_destroy(c); return code; };
   {
-    cudaError_t ee = cudaHostAlloc((void**)&c->hostAbort, sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable);
+    cudaError_t ee = cudaHostAlloc((void**)&c->hostOne, sizeof(int), cudaHostAllocPortable);
     if (ee != cudaSuccess) { c->err = std::string("cudaHostAlloc: ") + cudaGetErrorString(ee); return bail(HAVAC_CUDA_E_NOMEM); }
-    *c->hostAbort = 0;
+    *c->hostOne = 1;
   }
   for (int id : ids) {
     DeviceCtx d;
@@ -208,13 +210,14 @@ int havac_cuda_create(const char* deviceSpec, uint32_t deviceIndex, havac_cuda_c
     }
     d.numSMs = prop.multiProcessorCount;
     if (!ck(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
+        !ck(cudaStreamCreateWithFlags(&d.ctlStream, cudaStreamNonBlocking), "cudaStreamCreate") ||
         !ck(cudaEventCreate(&d.evStart), "cudaEventCreate") || !ck(cudaEventCreate(&d.evStop), "cudaEventCreate"))
       return bail(HAVAC_CUDA_E_RUNTIME);
     // the hit buffers are allocated once, like HavacHwClient::allocateOutputBuffers (HavacHwClient.cpp:73-76)
     if (!ck(cudaMalloc(&d.dHits, c->hitCap * sizeof(unsigned long long)), "cudaMalloc(hits)") ||
         !ck(cudaMalloc(&d.dHitCount, sizeof(unsigned long long)), "cudaMalloc") ||
         !ck(cudaMalloc(&d.dTileCounter, sizeof(unsigned int)), "cudaMalloc") ||
-        !ck(cudaMalloc(&d.dStatus, sizeof(int)), "cudaMalloc"))
+        !ck(cudaMalloc(&d.dStatus, sizeof(int)), "cudaMalloc") || !ck(cudaMalloc(&d.dAbort, sizeof(int)), "cudaMalloc"))
       return bail(HAVAC_CUDA_E_NOMEM);
   }
   *out = c;
@@ -223,9 +226,10 @@ int havac_cuda_create(const char* deviceSpec, uint32_t deviceIndex, havac_cuda_c
 
 int havac_cuda_destroy(havac_cuda_client* c) {
   if (!c) return HAVAC_CUDA_E_INVALID;
-  if (c->hostAbort) *c->hostAbort = 1;  // let a still-running kernel drain quickly
   for (DeviceCtx& d : c->devs) {
     cudaSetDevice(d.dev);
+    if (c->launched && !c->finished && d.dAbort && d.ctlStream)  // let a still-running kernel drain quickly
+      cudaMemcpyAsync(d.dAbort, c->hostOne, sizeof(int), cudaMemcpyHostToDevice, d.ctlStream);
     if (d.stream) cudaStreamSynchronize(d.stream);
     free_sequence(d);
     free_table(d);
@@ -233,11 +237,13 @@ int havac_cuda_destroy(havac_cuda_client* c) {
     if (d.dHitCount) cudaFree(d.dHitCount);
     if (d.dTileCounter) cudaFree(d.dTileCounter);
     if (d.dStatus) cudaFree(d.dStatus);
+    if (d.dAbort) cudaFree(d.dAbort);
+    if (d.ctlStream) cudaStreamDestroy(d.ctlStream);
     if (d.evStart) cudaEventDestroy(d.evStart);
     if (d.evStop) cudaEventDestroy(d.evStop);
     if (d.stream) cudaStreamDestroy(d.stream);
   }
-  if (c->hostAbort) cudaFreeHost(c->hostAbort);
+  if (c->hostOne) cudaFreeHost(c->hostOne);
   delete c;
   return HAVAC_CUDA_OK;
 }
@@ -323,13 +329,13 @@ int havac_cuda_invoke_async(havac_cuda_client* c) {
   if (c->seqSegments == 0) return fail(c, HAVAC_CUDA_E_LENGTH, "sequence length in segments cannot be 0, but 0 was given to the client.");
   if (c->nRows == 0) return fail(c, HAVAC_CUDA_E_LENGTH, "phmm length in vectors cannot be 0, but 0 was given to the client.");
   if (c->launched && !c->finished) return fail(c, HAVAC_CUDA_E_LOGIC, "a run is already in flight");
-  *c->hostAbort = 0;
   c->launches = 0;
   for (DeviceCtx& d : c->devs) {
     CK(cudaSetDevice(d.dev));
     CK(cudaMemsetAsync(d.dHitCount, 0, sizeof(unsigned long long), d.stream));
     CK(cudaMemsetAsync(d.dTileCounter, 0, sizeof(unsigned int), d.stream));
     CK(cudaMemsetAsync(d.dStatus, 0, sizeof(int), d.stream));
+    CK(cudaMemsetAsync(d.dAbort, 0, sizeof(int), d.stream));
     CK(cudaEventRecord(d.evStart, d.stream));
     if (d.colEnd > d.colBegin) {
       SsvParams p{};
@@ -352,9 +358,7 @@ int havac_cuda_invoke_async(havac_cuda_client* c) {
       p.hitCap = c->hitCap;
       p.hitCount = d.dHitCount;
       p.tileCounter = d.dTileCounter;
-      int* devAbort = nullptr;
-      CK(cudaHostGetDevicePointer((void**)&devAbort, c->hostAbort, 0));
-      p.abortFlag = devAbort;
+      p.abortFlag = d.dAbort;
       p.status = d.dStatus;
       if (c->kernel == KERNEL_SCALAR) ssv_launch_scalar(p, d.stream);
       else ssv_launch_f16x2(p, d.numSMs, d.stream);
@@ -419,7 +423,12 @@ int havac_cuda_abort(havac_cuda_client* c, int* state) {
   if (!c) return HAVAC_CUDA_E_INVALID;
   if (!c->launched) return fail(c, HAVAC_CUDA_E_LOGIC, "nothing was launched");
   if (!c->finished) {
-    *c->hostAbort = 1;
+    for (DeviceCtx& d : c->devs) {
+      CK(cudaSetDevice(d.dev));
+      // wait until the run has actually started, or the memset that opens it would clear the flag
+      CK(cudaEventSynchronize(d.evStart));
+      CK(cudaMemcpyAsync(d.dAbort, c->hostOne, sizeof(int), cudaMemcpyHostToDevice, d.ctlStream));
+    }
     int rc = collect(c);
     if (rc) return rc;
   }

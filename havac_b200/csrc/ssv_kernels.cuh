@@ -27,7 +27,7 @@ struct SsvParams {
   unsigned long long hitCap;
   unsigned long long* hitCount;  // total hits found (may exceed hitCap -> overflow)
   unsigned int* tileCounter;
-  const volatile int* abortFlag;  // host-mapped; non-zero = stop taking tiles
+  const volatile int* abortFlag;  // device memory; non-zero = stop (written by the host on a side stream)
   int* status;                    // bit 0: hit buffer overflow, bit 1: aborted
 };
 
