@@ -68,6 +68,7 @@ struct havac_cuda_client {
   int kernel = KERNEL_AUTO;
   uint32_t launches = 0;
   float lastMs = 0.f;
+  uint64_t h2dBytes = 0, d2hBytes = 0;  // running totals of what crossed PCIe
 };
 
 namespace {
@@ -146,6 +147,7 @@ int collect(havac_cuda_client* c) {
     CK(cudaEventSynchronize(d.evStop));
     CK(cudaMemcpy(&d.hitCount, d.dHitCount, sizeof d.hitCount, cudaMemcpyDeviceToHost));
     CK(cudaMemcpy(&d.status, d.dStatus, sizeof d.status, cudaMemcpyDeviceToHost));
+    c->d2hBytes += sizeof d.hitCount + sizeof d.status;
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, d.evStart, d.evStop));
     worst = std::max(worst, ms);
@@ -285,6 +287,7 @@ int havac_cuda_write_sequence(havac_cuda_client* c, const uint8_t* packed, uint6
     CK(cudaSetDevice(d.dev));
     CK(cudaMalloc(&d.dSeq, bytes));
     CK(cudaMemcpyAsync(d.dSeq, packed + d.resBegin / 4, bytes, cudaMemcpyHostToDevice, d.stream));
+    c->h2dBytes += bytes;
   }
   for (DeviceCtx& d : c->devs) {  // the reference's bo.sync is blocking too (HavacHwClient.cpp:104)
     CK(cudaSetDevice(d.dev));
@@ -313,6 +316,7 @@ int havac_cuda_write_phmm(havac_cuda_client* c, const int8_t* flat, uint64_t nBy
     CK(cudaMalloc(&d.dTab8, nBytes));
     CK(cudaMalloc(&d.dTab16, (size_t)d.rowsPadded * sizeof(uint2)));
     CK(cudaMemcpyAsync(d.dTab8, flat, nBytes, cudaMemcpyHostToDevice, d.stream));
+    c->h2dBytes += nBytes;
     ssv_launch_table_prep(d.dTab8, c->nRows, d.dTab16, d.rowsPadded, d.stream);
     CK(cudaGetLastError());
   }
@@ -460,6 +464,7 @@ int havac_cuda_read_hits(havac_cuda_client* c, uint64_t* out, uint64_t cap, uint
     if (!d.hitCount) continue;
     CK(cudaSetDevice(d.dev));
     CK(cudaMemcpy(out + off, d.dHits, d.hitCount * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    c->d2hBytes += d.hitCount * sizeof(uint64_t);
     off += d.hitCount;
   }
   // the FPGA emits hits by (segment, row, cell) ascending (device/HavacHls.cpp:131-162 outer loop
@@ -495,6 +500,13 @@ int havac_cuda_run_stats(havac_cuda_client* c, uint64_t* cells, uint32_t* launch
   for (DeviceCtx& d : c->devs) cols += (uint64_t)(d.colEnd - d.colBegin);
   if (cells) *cells = cols * c->nRows;
   if (launches) *launches = c->launches;
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_transfer_stats(havac_cuda_client* c, uint64_t* h2d, uint64_t* d2h) {
+  if (!c) return HAVAC_CUDA_E_INVALID;
+  if (h2d) *h2d = c->h2dBytes;
+  if (d2h) *d2h = c->d2hBytes;
   return HAVAC_CUDA_OK;
 }
 

@@ -192,3 +192,37 @@ def random_packed(seed: int, n_symbols: int) -> np.ndarray:
     for k in range(nb * 4, n_symbols):
         out[k >> 2] |= np.uint8(int(g.integers(0, 4)) << ((k & 3) * 2))
     return out
+
+
+def consensus_score_table(seed: int, n_rows: int, hi: Tuple[int, int] = (14, 22),
+                          lo: Tuple[int, int] = (-32, -9)) -> Tuple[np.ndarray, np.ndarray]:
+    """An int8 [row][A,C,G,T] score table shaped like a projected nucleotide model (one
+    positive consensus score per row, three negative ones; PhmmReprojection.cpp:109-145 at
+    p = 0.02 gives these ranges for the random models above) without going through a .hmm
+    file. Returns (table, consensus symbols)."""
+    g = rng(seed, 77)
+    t = g.integers(lo[0], lo[1] + 1, size=(n_rows, 4)).astype(np.int8)
+    cons = g.integers(0, 4, size=n_rows)
+    t[np.arange(n_rows), cons] = g.integers(hi[0], hi[1] + 1, size=n_rows)
+    return t, cons.astype(np.uint8)
+
+
+def plant_consensus(seed: int, symbols: np.ndarray, consensus: np.ndarray, copies: int,
+                    substitution: float = 0.1, min_len: int = 40) -> int:
+    """Overwrite ``copies`` windows of ``symbols`` with mutated fragments of ``consensus``
+    (the role of test/generator/hmmSeqGenerator.cpp:72-84). Returns how many were placed."""
+    g = rng(seed, 78)
+    n, L = len(symbols), len(consensus)
+    placed = 0
+    for _ in range(copies):
+        a = int(g.integers(0, L - min_len)) if L > 2 * min_len else 0
+        b = int(g.integers(a + min_len, L + 1)) if L > 2 * min_len else L
+        frag = consensus[a:b].copy()
+        mut = g.random(len(frag)) < substitution
+        frag[mut] = g.integers(0, 4, size=int(mut.sum()))
+        if len(frag) >= n:
+            continue
+        at = int(g.integers(0, n - len(frag)))
+        symbols[at:at + len(frag)] = frag
+        placed += 1
+    return placed

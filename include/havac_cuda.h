@@ -108,6 +108,8 @@ int havac_cuda_device_count(havac_cuda_client* c, int* n);
 /* Per-run facts for roofline accounting: cells = real cells computed (rows x columns
  * of this client's range, halo and padding excluded); launches = kernels launched. */
 int havac_cuda_run_stats(havac_cuda_client* c, uint64_t* cells, uint32_t* launches);
+/* Running totals of the bytes this client copied host->device and device->host. */
+int havac_cuda_transfer_stats(havac_cuda_client* c, uint64_t* h2dBytes, uint64_t* d2hBytes);
 /* Select a kernel variant by name ("auto" | "f16x2" | "scalar"); for tests that
  * cross-check the fast path against the plain one. */
 int havac_cuda_set_kernel(havac_cuda_client* c, const char* name);

@@ -132,3 +132,31 @@ def ref_load_fasta(path, seed=1):
     ends = np.zeros(ns.value, dtype=np.uint64)
     L.ref_load_fasta(path.encode(), seed, packed.ctypes.data, nb, ends.ctypes.data, ns.value, C.byref(ns), C.byref(cnt))
     return packed, ends, cnt.value
+
+
+def soft_ssv_parallel(symbols, table, threads, lib=None, cap=1 << 20):
+    """The same SSV on `threads` host threads: the sequence axis is cut into chunks, each run
+    with a left halo of rows-1 symbols and its halo hits discarded (exact: a cell depends only
+    on its own diagonal, which starts at row 0 at most rows-1 columns to the left; SURVEY.md
+    section 8e). ctypes releases the GIL during the call, so plain threads scale."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    symbols = np.ascontiguousarray(symbols, dtype=np.uint8)
+    table = np.ascontiguousarray(table, dtype=np.int8).reshape(-1, 4)
+    n, rows = len(symbols), table.shape[0]
+    threads = max(1, min(int(threads), max(1, n // 1024)))
+    edges = [n * i // threads for i in range(threads + 1)]
+
+    def work(i):
+        a, b = edges[i], edges[i + 1]
+        lo = max(0, a - (rows - 1))
+        pos, row = soft_ssv(symbols[lo:b], table, lib=lib, cap=cap)
+        pos = pos + np.uint64(lo)
+        keep = pos >= np.uint64(a)
+        return pos[keep], row[keep]
+
+    if threads == 1:
+        return work(0)
+    with ThreadPoolExecutor(threads) as ex:
+        parts = list(ex.map(work, range(threads)))
+    return np.concatenate([p for p, _ in parts]), np.concatenate([r for _, r in parts])
