@@ -270,13 +270,20 @@ def run_gpu(args, rank, world, local_rank):
     value = cells_all / (ms_dev * 1e-3) / 1e9
 
     # ---- end to end through the client calls with host buffers ----------------------------
+    phases = {}
+
     def e2e_step():
-        client.writeSequence(packed)
-        client.writePhmm(table)
+        t = [time.perf_counter()]
+        client.writeSequence(packed); t.append(time.perf_counter())
+        client.writePhmm(table); t.append(time.perf_counter())
         client.invokeHavacSsvAsync()
         if client.waitForHavacSsvAsync() != STATE_COMPLETED:
             raise RuntimeError("e2e run did not complete")
-        return client.getHitList()
+        t.append(time.perf_counter())
+        h = client.getHitList(); t.append(time.perf_counter())
+        for name, a, b in zip(("writeSequence", "writePhmm", "run", "getHitList"), t, t[1:]):
+            phases[name] = round((b - a) * 1e3, 3)
+        return h
 
     e2e_step()
     h2d0, d2h0 = client.transferStats()
@@ -287,6 +294,7 @@ def run_gpu(args, rank, world, local_rank):
     barrier()
     e2e_s = reduce_max((time.perf_counter() - t0) / args.steps)
     h2d1, d2h1 = client.transferStats()
+    log(f"[rank {rank}] e2e phases of the last step (ms): {phases}")
     e2e_val = cells_all / e2e_s / 1e9
     h2d = reduce_sum(float(h2d1 - h2d0)) / args.steps
     d2h = reduce_sum(float(d2h1 - d2h0)) / args.steps
@@ -333,7 +341,7 @@ def run_gpu(args, rank, world, local_rank):
                        "symbols_per_gpu": SEQ_PER_GPU, "rows": rows, "hits": int(hits_all),
                        "parallelism": f"sequence axis sharded over {world} GPU(s), halo rows-1, no collective"},
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "ms_per_step": e2e_s * 1e3},
+                    "ms_per_step": e2e_s * 1e3, "phases_ms": phases},
             "gpu_launches": int(launches_per_step * args.steps * world),
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "published_fpga_gcups": 1739,

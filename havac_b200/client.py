@@ -28,7 +28,7 @@ EXPORTS = [
     "havac_cuda_create", "havac_cuda_destroy", "havac_cuda_write_sequence", "havac_cuda_write_phmm",
     "havac_cuda_set_segment_range", "havac_cuda_invoke_async", "havac_cuda_state", "havac_cuda_wait",
     "havac_cuda_abort", "havac_cuda_num_hits", "havac_cuda_read_hits", "havac_cuda_last_error",
-    "havac_cuda_device_time_ms", "havac_cuda_device_count", "havac_cuda_run_stats", "havac_cuda_set_kernel", "havac_cuda_transfer_stats",
+    "havac_cuda_device_time_ms", "havac_cuda_device_count", "havac_cuda_run_stats", "havac_cuda_set_kernel", "havac_cuda_transfer_stats", "havac_cuda_sm_cycles",
 ]
 
 
@@ -71,6 +71,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     L.havac_cuda_device_count.argtypes = [vp, C.POINTER(C.c_int)]
     L.havac_cuda_run_stats.argtypes = [vp, C.POINTER(u64), C.POINTER(u32)]
     L.havac_cuda_set_kernel.argtypes = [vp, C.c_char_p]
+    L.havac_cuda_sm_cycles.argtypes = [vp, C.POINTER(u64)]
     L.havac_cuda_transfer_stats.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
     for name in EXPORTS:
         if name != "havac_cuda_last_error":
@@ -169,6 +170,11 @@ class HavacHwClient:
         cells, launches = C.c_uint64(0), C.c_uint32(0)
         self._ck(self._L.havac_cuda_run_stats(self._h, C.byref(cells), C.byref(launches)))
         return cells.value, launches.value
+
+    def smCycles(self) -> int:
+        n = C.c_uint64(0)
+        self._ck(self._L.havac_cuda_sm_cycles(self._h, C.byref(n)))
+        return n.value
 
     def transferStats(self):
         a, b = C.c_uint64(0), C.c_uint64(0)

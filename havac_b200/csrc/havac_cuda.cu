@@ -46,6 +46,8 @@ struct DeviceCtx {
   unsigned long long* dHitCount = nullptr;
   unsigned int* dTileCounter = nullptr;
   int* dStatus = nullptr;
+  unsigned long long* dCycles = nullptr;  // SM cycles of CTA 0 in the last run
+  unsigned long long cycles = 0;
   int* dAbort = nullptr;          // device-resident abort flag the kernels poll (L2 hit, no PCIe)
   cudaStream_t ctlStream = nullptr;  // carries the abort write while the run stream is busy
   // results of the last finished run
@@ -147,6 +149,7 @@ int collect(havac_cuda_client* c) {
     CK(cudaEventSynchronize(d.evStop));
     CK(cudaMemcpy(&d.hitCount, d.dHitCount, sizeof d.hitCount, cudaMemcpyDeviceToHost));
     CK(cudaMemcpy(&d.status, d.dStatus, sizeof d.status, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(&d.cycles, d.dCycles, sizeof d.cycles, cudaMemcpyDeviceToHost));
     c->d2hBytes += sizeof d.hitCount + sizeof d.status;
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, d.evStart, d.evStop));
@@ -219,7 +222,8 @@ int havac_cuda_create(const char* deviceSpec, uint32_t deviceIndex, havac_cuda_c
     if (!ck(cudaMalloc(&d.dHits, c->hitCap * sizeof(unsigned long long)), "cudaMalloc(hits)") ||
         !ck(cudaMalloc(&d.dHitCount, sizeof(unsigned long long)), "cudaMalloc") ||
         !ck(cudaMalloc(&d.dTileCounter, sizeof(unsigned int)), "cudaMalloc") ||
-        !ck(cudaMalloc(&d.dStatus, sizeof(int)), "cudaMalloc") || !ck(cudaMalloc(&d.dAbort, sizeof(int)), "cudaMalloc"))
+        !ck(cudaMalloc(&d.dStatus, sizeof(int)), "cudaMalloc") ||
+        !ck(cudaMalloc(&d.dCycles, sizeof(unsigned long long)), "cudaMalloc") || !ck(cudaMalloc(&d.dAbort, sizeof(int)), "cudaMalloc"))
       return bail(HAVAC_CUDA_E_NOMEM);
   }
   *out = c;
@@ -239,6 +243,7 @@ int havac_cuda_destroy(havac_cuda_client* c) {
     if (d.dHitCount) cudaFree(d.dHitCount);
     if (d.dTileCounter) cudaFree(d.dTileCounter);
     if (d.dStatus) cudaFree(d.dStatus);
+    if (d.dCycles) cudaFree(d.dCycles);
     if (d.dAbort) cudaFree(d.dAbort);
     if (d.ctlStream) cudaStreamDestroy(d.ctlStream);
     if (d.evStart) cudaEventDestroy(d.evStart);
@@ -339,6 +344,7 @@ int havac_cuda_invoke_async(havac_cuda_client* c) {
     CK(cudaMemsetAsync(d.dHitCount, 0, sizeof(unsigned long long), d.stream));
     CK(cudaMemsetAsync(d.dTileCounter, 0, sizeof(unsigned int), d.stream));
     CK(cudaMemsetAsync(d.dStatus, 0, sizeof(int), d.stream));
+    CK(cudaMemsetAsync(d.dCycles, 0, sizeof(unsigned long long), d.stream));
     CK(cudaMemsetAsync(d.dAbort, 0, sizeof(int), d.stream));
     CK(cudaEventRecord(d.evStart, d.stream));
     if (d.colEnd > d.colBegin) {
@@ -364,6 +370,7 @@ int havac_cuda_invoke_async(havac_cuda_client* c) {
       p.tileCounter = d.dTileCounter;
       p.abortFlag = d.dAbort;
       p.status = d.dStatus;
+      p.smCycles = d.dCycles;
       if (c->kernel == KERNEL_SCALAR) ssv_launch_scalar(p, d.stream);
       else ssv_launch_f16x2(p, d.numSMs, d.stream);
       CK(cudaGetLastError());
@@ -500,6 +507,17 @@ int havac_cuda_run_stats(havac_cuda_client* c, uint64_t* cells, uint32_t* launch
   for (DeviceCtx& d : c->devs) cols += (uint64_t)(d.colEnd - d.colBegin);
   if (cells) *cells = cols * c->nRows;
   if (launches) *launches = c->launches;
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_sm_cycles(havac_cuda_client* c, uint64_t* cycles) {
+  if (!c || !cycles) return HAVAC_CUDA_E_INVALID;
+  if (!c->launched) return fail(c, HAVAC_CUDA_E_LOGIC, "nothing was launched");
+  int rc = collect(c);
+  if (rc) return rc;
+  uint64_t worst = 0;
+  for (DeviceCtx& d : c->devs) worst = std::max<uint64_t>(worst, d.cycles);
+  *cycles = worst;
   return HAVAC_CUDA_OK;
 }
 

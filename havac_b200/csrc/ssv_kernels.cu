@@ -11,8 +11,8 @@
 //    All values are multiples of 256 below 2^16, so fp16 arithmetic is exact; a negative sum is
 //    clamped by .RELU (the reset-to-zero of HavacHls.cpp:382); a sum >= 256*256 = 65536
 //    overflows fp16 to +inf, and inf is sticky under further adds. A hit is therefore never
-//    lost: each thread looks for inf once per 32-row block and, if it finds one, replays that
-//    block from a saved copy with exact integer arithmetic (which also performs the reset that
+//    lost: each thread looks for inf once per superblock and, if it finds one, replays that
+//    superblock from a checkpoint with exact integer arithmetic (which also performs the reset that
 //    follows a hit). Hits are ~1e-7 per cell, so the replay is off the critical path.
 //  * The emission lookup e[p][x_j] for two cells is ONE PRMT: the row's four fp16 scores sit
 //    in two registers (8 bytes) and the per-symbol selector byte 0x10+0x22*x picks the two
@@ -23,8 +23,12 @@
 //    memory-bound: per 8192-diagonal row it reads 8 B of table and 1/4 B of sequence.
 //  * Score-table rows are staged into shared memory in 512-row chunks by TMA bulk copies
 //    (cp.async.bulk + mbarrier, double buffered). The 2-bit packed sequence is read from HBM
-//    with coalesced 128-bit loads, one chunk ahead, and expanded to selector bytes in a
-//    shared-memory ring that slides along the diagonal band.
+//    one chunk ahead and expanded into a shared-memory ring of ready-made selector windows
+//    (one 32-bit entry per symbol) that slides along the diagonal band; a thread fetches the
+//    four windows of four rows with one conflict-free LDS.128, so the hot loop spends no ALU
+//    instruction on selectors.
+//  * The state at the start of every 128-row superblock is checkpointed in shared memory;
+//    hits (inf) are looked for once per superblock.
 //  * Hits are compacted with warp ballot + prefix popcount and one atomicAdd per warp-row.
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
@@ -115,18 +119,30 @@ constexpr int R = SSV_R;
 constexpr int THREADS = SSV_THREADS;
 constexpr int W = SSV_TILE_DIAGS;
 constexpr int TC = SSV_ROW_CHUNK;
-constexpr int BLOCK_ROWS = SSV_BLOCK_ROWS;
-constexpr int PAD = 64;              // symbols the ring stays ahead of the furthest reader
-constexpr int RING = 16384;          // bytes; power of two >= W + 2*TC + PAD
-constexpr int RING_MASK = RING - 1;
-static_assert(W + 2 * TC + PAD <= RING, "ring too small");
-static_assert(TC % BLOCK_ROWS == 0, "row chunk must hold whole blocks");
-static_assert(TC / 64 <= 32, "chunk refill is done by one warp");
+constexpr int BLOCK_ROWS = SSV_BLOCK_ROWS;          // rows unrolled in one block (= 2R = 32)
+constexpr int SB_BLOCKS = SSV_SUPERBLOCK_BLOCKS;    // blocks between two hit checks / checkpoints
+constexpr int SB_ROWS = SB_BLOCKS * BLOCK_ROWS;
+constexpr int NSLOT = (W + 2 * TC) / 32;            // 32-symbol groups the window ring holds
+static_assert(BLOCK_ROWS == 32 && R == 16, "the ring layout assumes 32 diagonals and 32 rows per thread-block");
+static_assert(TC % SB_ROWS == 0, "row chunk must hold whole superblocks");
+static_assert(TC / 16 <= 32, "chunk refill is done by one warp");
+static_assert((W + 2 * TC) % 32 == 0, "ring must hold whole 32-symbol groups");
 
+// Shared memory of one CTA (dynamic; ~60 KB, two CTAs per SM).
+//  ring : selector WINDOWS, one 32-bit entry per symbol. The entry of symbol j is
+//         sel(x_j) | sel(x_j+1) << 8 | ..., sel(x) = 0x10 + 0x22 x; PRMT reads bits [15:0], which
+//         pick the fp16 scores of x_j and x_j+1 out of the 8-byte table row. Symbol offset
+//         s = j - D0 lives at ring[(s & 31) >> 2][(s >> 5) % NSLOT] component s & 3, so the four
+//         windows a thread needs for four consecutive rows are one LDS.128, and the 32 lanes of a
+//         warp (32 symbols apart) read 32 consecutive uint4 -- conflict-free.
+//  tab  : double-buffered score-table chunks (TMA bulk copies).
+//  ckpt : the thread's 16 state registers at the start of the current superblock, for the exact
+//         replay (kept in shared memory so the hot loop carries no copies of them).
 struct __align__(16) FastSmem {
-  uint8_t ring[RING];          // selector bytes 0x10 + 0x22*x, ring[(j - D0) & RING_MASK]
-  uint2 tab[2][TC];            // double-buffered score-table chunks
-  unsigned long long mbar[2];  // TMA completion barriers
+  uint4 ring[8][NSLOT];
+  uint2 tab[2][TC];
+  uint4 ckpt[R / 4][THREADS];
+  unsigned long long mbar[2];
   unsigned int nextTile;
   int abortSeen;
 };
@@ -184,6 +200,26 @@ __device__ __forceinline__ uint32_t load_seq_word(const SsvParams& prm, long lon
   return (wi >= 0 && wi < nWords) ? __ldg(prm.seqPacked + wi) : 0u;
 }
 
+// Write the 16 window entries of the symbols in packed word `x` (symbol offsets s .. s+15 from
+// the tile's first diagonal, s a multiple of 16); `xNext` is the following packed word, whose
+// first symbol completes the last window.
+__device__ __forceinline__ void ring_fill16(FastSmem& sm, uint32_t s, uint32_t x, uint32_t xNext) {
+  const uint4 o = expand16(x);
+  const uint32_t o4 = 0x10u + 0x22u * (xNext & 3u);
+  const uint32_t ow[5] = {o.x, o.y, o.z, o.w, o4};
+  const uint32_t slot = (s >> 5) % (uint32_t)NSLOT;
+  const uint32_t plane0 = (s & 31u) >> 2;  // 0 or 4
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    uint4 v;
+    v.x = ow[q];
+    v.y = __funnelshift_r(ow[q], ow[q + 1], 8);
+    v.z = __funnelshift_r(ow[q], ow[q + 1], 16);
+    v.w = __funnelshift_r(ow[q], ow[q + 1], 24);
+    sm.ring[plane0 + q][slot] = v;
+  }
+}
+
 // PRMT with the raw PTX semantics (CUDA's __byte_perm would first AND the selector with
 // 0x7777). Only selector bits [15:0] are read; our nibbles are all <= 7 (plain byte copy).
 __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
@@ -204,96 +240,122 @@ __device__ __forceinline__ bool has_inf(uint32_t v) {
   return ((v + 0x04000400u) & 0x80008000u) != 0u;
 }
 
-// Exact integer replay of one 32-row block for the registers of this thread that need it.
-// Warp-convergent: every lane runs the same trip counts, lanes without work idle, so the
-// ballot-based hit compaction inside is legal.
-//   sv   : state at the start of the block (fp16x2)      w : state to overwrite with the result
-//   need : per-thread "replay every register" flag (left-edge band); otherwise registers are
-//          replayed when their fast-path result holds an inf.
-__device__ __noinline__ void exact_block(const SsvParams& prm, const FastSmem& sm, const uint2* tab,
-                                         const uint32_t (&sv)[R], uint32_t (&w)[R], bool needAll,
-                                         long long d0, long long D0, uint32_t pb) {
-#pragma unroll
+// Hit emission from divergent code: the lanes that are here together aggregate into one atomic
+// (ballot of the active lanes + prefix popcount for the slot).
+__device__ __forceinline__ void emit_hit_active(const SsvParams& prm, long long col, uint32_t row) {
+  const unsigned m = __activemask();
+  const unsigned lane = threadIdx.x & 31;
+  const int leader = __ffs(m) - 1;
+  unsigned long long base = 0;
+  if ((int)lane == leader) base = atomicAdd(prm.hitCount, (unsigned long long)__popc(m));
+  base = __shfl_sync(m, base, leader);
+  const unsigned long long slot = base + __popc(m & ((1u << lane) - 1));
+  if (slot < prm.hitCap) prm.hits[slot] = encode_hit(col, row);
+  else atomicOr(prm.status, SSV_STATUS_OVERFLOW);
+}
+
+// Exact replay of one superblock (nRowsReplay rows from row pb) for the registers of this
+// thread that need it, starting from the checkpoint in shared memory. It is the same fp16x2
+// cell update as the fast path, one row at a time, with the overflow looked at after every row:
+// 256 (s + e) rounds to +inf exactly when s + e >= 256, so "inf" IS the hit test of
+// SoftSsv.cpp:44 / HavacHls.cpp:386, and the half that hit is reset to 0 as the reference does.
+// Lanes and registers with nothing to do skip; no warp-synchronous call is made in here.
+//   w    : fast-path result; replayed registers are overwritten with the exact state
+//   edge : the tile still has diagonals left of column 0 in this superblock. Registers wholly
+//          left of it are zeroed (nothing real yet: prev score is 0 at column 0, SoftSsv.cpp:37),
+//          registers crossing it are replayed with the cells left of column 0 held at 0.
+__device__ __noinline__ void exact_rows(const SsvParams& prm, const FastSmem& sm, const uint2* tab,
+                                        uint32_t (&w)[R], bool edge, long long d0, long long D0,
+                                        uint32_t pb, uint32_t nRowsReplay) {
+  const uint32_t* ck = reinterpret_cast<const uint32_t*>(&sm.ckpt[0][0]);
+#pragma unroll 1
   for (int k = 0; k < R; k++) {
-    bool need = needAll || has_inf(w[k]);
-    if (!__any_sync(FULL, need)) continue;
-    uint32_t res = 0;
-#pragma unroll 1
-    for (int h = 0; h < 2; h++) {
-      int s = __half2int_rn(__ushort_as_half((unsigned short)(sv[k] >> (16 * h)))) >> 8;
-      long long d = d0 + 2 * k + h;
-#pragma unroll 1
-      for (int r = 0; r < BLOCK_ROWS; r++) {
-        uint32_t p = pb + r;
-        long long j = d + p;
-        bool hit = false;
-        if (need) {
-          if (j < 0) {
-            s = 0;  // column left of the sequence start: prev score is 0 (SoftSsv.cpp:37)
-          } else {
-            uint32_t x = sm.ring[(uint32_t)(j - D0) & RING_MASK] >> 5;
-            uint2 e2 = tab[p & (TC - 1)];
-            uint32_t eh = ((x & 2) ? e2.y : e2.x) >> (16 * (x & 1));
-            s += __half2int_rn(__ushort_as_half((unsigned short)eh)) >> 8;
-            if (s < 0) s = 0;
-            else if (s >= 256) { s = 0; hit = true; }
-          }
-        }
-        long long col = j + prm.loadBegin;
-        hit = hit && p < prm.nRows && col >= prm.colBegin && col < prm.colEnd;
-        emit_hits_warp(prm, hit, col, p);
+    const long long dlo = d0 + 2 * k;  // diagonals dlo (low half) and dlo + 1 (high half)
+    bool crossing = false;
+    if (edge) {
+      if (dlo + 1 + (long long)pb + nRowsReplay - 1 < 0) {  // wholly left of column 0
+        w[k] = 0u;
+        continue;
       }
-      res |= (uint32_t)__half_as_ushort(__int2half_rn(s * 256)) << (16 * h);
+      crossing = dlo + (long long)pb < 0;
     }
-    if (need) w[k] = res;
+    if (!crossing && !has_inf(w[k])) continue;
+    uint32_t v = ck[((k >> 2) * THREADS + threadIdx.x) * 4 + (k & 3)];
+    const uint32_t s0 = (uint32_t)(dlo + (long long)pb - D0);  // ring offset of the low half's symbol at row pb
+#pragma unroll 4
+    for (uint32_t r = 0; r < nRowsReplay; r++) {
+      const uint32_t s = s0 + r;
+      const uint32_t* words = reinterpret_cast<const uint32_t*>(&sm.ring[(s & 31u) >> 2][(s >> 5) % (uint32_t)NSLOT]);
+      const uint32_t sel = words[s & 3u];
+      const uint32_t p = pb + r;
+      const uint2 e2 = tab[p & (TC - 1)];
+      v = hfma2_relu_add(prmt(e2.x, e2.y, sel), v);
+      if (crossing) {  // cells left of column 0 do not exist
+        const long long j = dlo + (long long)p;
+        if (j < 0) v &= 0xffff0000u;
+        if (j + 1 < 0) v = 0u;
+      }
+      if (has_inf(v)) {
+#pragma unroll 1
+        for (int h = 0; h < 2; h++) {
+          if (((v >> (16 * h)) & 0xffffu) != 0x7c00u) continue;
+          v &= h ? 0x0000ffffu : 0xffff0000u;
+          const long long col = dlo + h + (long long)p + prm.loadBegin;
+          if (p < prm.nRows && col >= prm.colBegin && col < prm.colEnd) emit_hit_active(prm, col, p);
+        }
+      }
+    }
+    w[k] = v;
   }
 }
 
-// One 4-row group of the fast path. u = group index inside the 32-row block (compile time),
+// One 4-row group of the fast path. U = group index inside the 32-row block (compile time),
 // so every register index below is static after unrolling.
+//   rows 4U+0..3 -> (q, c) = (2U,0) (2U,1) (2U+1,0) (2U+1,1)
+//   register k at row r needs the window of symbol d0 + 2k + r: even rows read e0, odd rows e1,
+//   and the slot a row just finished with is refilled with the window 32 symbols further on.
 template <int U>
 __device__ __forceinline__ void four_rows(uint32_t (&w)[R], uint32_t (&e0)[R], uint32_t (&e1)[R],
-                                          const uint2* __restrict__ tabRow, uint32_t wn,
-                                          uint32_t wn1) {
-  // rows 4U+0..3  ->  (q, c) = (2U,0) (2U,1) (2U+1,0) (2U+1,1)
+                                          const uint2* __restrict__ tabRow,
+                                          const uint4* __restrict__ ringSlot) {
+  const uint4 win = ringSlot[U * NSLOT];                                    // windows of the next block
   const uint4 ab01 = *reinterpret_cast<const uint4*>(tabRow + 4 * U);      // rows 4U, 4U+1
   const uint4 ab23 = *reinterpret_cast<const uint4*>(tabRow + 4 * U + 2);  // rows 4U+2, 4U+3
   constexpr int Q0 = 2 * U, Q1 = 2 * U + 1;
 #pragma unroll
   for (int k = 0; k < R; k++) w[k] = hfma2_relu_add(prmt(ab01.x, ab01.y, e0[(Q0 + k) % R]), w[k]);
-  e0[Q0 % R] = wn;  // window at symbol b        (PRMT reads selector bits [15:0] only)
+  e0[Q0 % R] = win.x;
 #pragma unroll
   for (int k = 0; k < R; k++) w[k] = hfma2_relu_add(prmt(ab01.z, ab01.w, e1[(Q0 + k) % R]), w[k]);
-  e1[Q0 % R] = wn >> 8;  // window at b+1
+  e1[Q0 % R] = win.y;
 #pragma unroll
   for (int k = 0; k < R; k++) w[k] = hfma2_relu_add(prmt(ab23.x, ab23.y, e0[(Q1 + k) % R]), w[k]);
-  e0[Q1 % R] = wn >> 16;  // window at b+2
+  e0[Q1 % R] = win.z;
 #pragma unroll
   for (int k = 0; k < R; k++) w[k] = hfma2_relu_add(prmt(ab23.z, ab23.w, e1[(Q1 + k) % R]), w[k]);
-  e1[Q1 % R] = __funnelshift_r(wn, wn1, 24);  // window at b+3 (crosses into the next word)
+  e1[Q1 % R] = win.w;
 }
 
 template <int U>
 struct RowGroups {
   static __device__ __forceinline__ void run(uint32_t (&w)[R], uint32_t (&e0)[R], uint32_t (&e1)[R],
-                                             const uint2* tabRow, const uint8_t* ring,
-                                             uint32_t pos, uint32_t& wn) {
-    uint32_t wn1 = *reinterpret_cast<const uint32_t*>(ring + ((pos + 4 * (U + 1)) & RING_MASK));
-    four_rows<U>(w, e0, e1, tabRow, wn, wn1);
-    wn = wn1;
-    RowGroups<U + 1>::run(w, e0, e1, tabRow, ring, pos, wn);
+                                             const uint2* tabRow, const uint4* ringSlot) {
+    four_rows<U>(w, e0, e1, tabRow, ringSlot);
+    RowGroups<U + 1>::run(w, e0, e1, tabRow, ringSlot);
   }
 };
 template <>
 struct RowGroups<BLOCK_ROWS / 4> {
   static __device__ __forceinline__ void run(uint32_t (&)[R], uint32_t (&)[R], uint32_t (&)[R],
-                                             const uint2*, const uint8_t*, uint32_t, uint32_t&) {}
+                                             const uint2*, const uint4*) {}
 };
 
 __global__ void __launch_bounds__(THREADS, 2) ssv_f16x2_kernel(const SsvParams prm) {
-  __shared__ FastSmem sm;
+  extern __shared__ __align__(16) unsigned char smemRaw[];
+  FastSmem& sm = *reinterpret_cast<FastSmem*>(smemRaw);
   const int tid = threadIdx.x;
   uint32_t mbarPhase = 0;  // bit b = parity to wait for on sm.mbar[b]
+  const long long clk0 = clock64();
 
   if (tid == 0) {
     mbar_init(&sm.mbar[0], 1);
@@ -326,7 +388,7 @@ __global__ void __launch_bounds__(THREADS, 2) ssv_f16x2_kernel(const SsvParams p
       continue;
     }
 
-    // --- prologue: queue the first two table chunks, fill the ring, load selectors ---------
+    // --- prologue: queue the first two table chunks, fill the ring, load the windows --------
     if (tid == 0) {
       sm.nextTile = atomicAdd(prm.tileCounter, 1u);
       if (*prm.abortFlag) sm.abortSeen = 1;
@@ -335,82 +397,76 @@ __global__ void __launch_bounds__(THREADS, 2) ssv_f16x2_kernel(const SsvParams p
         tma_load_1d(sm.tab[i], prm.tab16 + (size_t)(c0 + i) * TC, TC * sizeof(uint2), &sm.mbar[i]);
       }
     }
-    const long long jFill0 = D0 + (long long)c0 * TC;  // first symbol the tile needs
-    for (int i = tid; i < (W + 2 * TC + PAD) / 16; i += THREADS) {
-      long long j = jFill0 + 16ll * i;
-      uint4 v = expand16(load_seq_word(prm, j >> 4));
-      *reinterpret_cast<uint4*>(sm.ring + ((uint32_t)(j - D0) & RING_MASK)) = v;
+    const uint32_t p0 = (uint32_t)c0 * TC;  // first row; ring holds offsets [p0, p0 + W + 2 TC)
+    {
+      const long long wFill0 = (D0 + (long long)p0) >> 4;  // D0 and p0 are multiples of 64
+      for (int i = tid; i < (W + 2 * TC) / 16; i += THREADS)
+        ring_fill16(sm, p0 + 16u * (uint32_t)i, load_seq_word(prm, wFill0 + i), load_seq_word(prm, wFill0 + i + 1));
     }
     __syncthreads();
 
-    uint32_t w[R], sv[R], e0[R], e1[R];
-    {
-      const uint32_t p0 = (uint32_t)c0 * TC;
-      const uint32_t base = (uint32_t)(tid * 2 * R) + p0;  // ring position of symbol d0 + p0
+    uint32_t w[R], e0[R], e1[R];
+    uint32_t g = ((uint32_t)tid + p0 / 32u) % (uint32_t)NSLOT;  // slot of symbol offset 32 tid + p0
 #pragma unroll
-      for (int n = 0; n < R; n += 2) {
-        uint32_t a = *reinterpret_cast<const uint32_t*>(sm.ring + ((base + 2 * n) & RING_MASK));
-        uint32_t b = *reinterpret_cast<const uint32_t*>(sm.ring + ((base + 2 * n + 4) & RING_MASK));
-        e0[n] = a;
-        e1[n] = a >> 8;
-        e0[n + 1] = a >> 16;
-        e1[n + 1] = __funnelshift_r(a, b, 24);
-      }
-#pragma unroll
-      for (int k = 0; k < R; k++) w[k] = 0u;
+    for (int u = 0; u < R / 2; u++) {
+      const uint4 v = sm.ring[u][g];
+      e0[2 * u] = v.x;
+      e1[2 * u] = v.y;
+      e0[2 * u + 1] = v.z;
+      e1[2 * u + 1] = v.w;
     }
+#pragma unroll
+    for (int k = 0; k < R; k++) w[k] = 0u;
+    g = (g + 1 == (uint32_t)NSLOT) ? 0u : g + 1;  // slot the first block loads its new windows from
 
     // --- main loop over row chunks -----------------------------------------------------------
     for (int c = c0; c < c1; c++) {
       const int buf = (c - c0) & 1;
-      // prefetch the packed symbols that extend the ring for chunk c+2 (consumed after compute)
-      uint4 refill = make_uint4(0, 0, 0, 0);
-      const long long jRefill = D0 + W + (long long)(c + 2) * TC + PAD;
-      if (tid < TC / 64 && c + 1 < c1) {
-        long long wi = (jRefill >> 4) + 4 * tid;
-        refill.x = load_seq_word(prm, wi);
-        refill.y = load_seq_word(prm, wi + 1);
-        refill.z = load_seq_word(prm, wi + 2);
-        refill.w = load_seq_word(prm, wi + 3);
+      // prefetch the packed symbols that extend the ring for chunk c+2 (written after compute)
+      uint32_t refill0 = 0, refill1 = 0;
+      const uint32_t sRefill = (uint32_t)W + (uint32_t)(c + 2) * TC;
+      const bool doRefill = tid < TC / 16 && c + 2 < c1;
+      if (doRefill) {
+        const long long wi = ((D0 + (long long)sRefill) >> 4) + tid;
+        refill0 = load_seq_word(prm, wi);
+        refill1 = load_seq_word(prm, wi + 1);
       }
       mbar_wait(&sm.mbar[buf], (mbarPhase >> buf) & 1u);
       mbarPhase ^= 1u << buf;
 
       long long chunkEnd = (long long)(c + 1) * TC;
       if (chunkEnd > rowEnd) chunkEnd = rowEnd;
-      for (uint32_t pb = (uint32_t)c * TC; (long long)pb < chunkEnd; pb += BLOCK_ROWS) {
+      for (uint32_t pb = (uint32_t)c * TC; (long long)pb < chunkEnd; pb += SB_ROWS) {
+        int nb = (int)((chunkEnd - (long long)pb + BLOCK_ROWS - 1) / BLOCK_ROWS);
+        if (nb > SB_BLOCKS) nb = SB_BLOCKS;
 #pragma unroll
-        for (int k = 0; k < R; k++) sv[k] = w[k];
-        const uint32_t pos = (uint32_t)(tid * 2 * R) + pb + 2 * R;  // ring position of d0+pb+2R
-        uint32_t wn = *reinterpret_cast<const uint32_t*>(sm.ring + (pos & RING_MASK));
-        RowGroups<0>::run(w, e0, e1, sm.tab[buf] + (pb & (TC - 1)), sm.ring, pos, wn);
+        for (int q = 0; q < R / 4; q++)
+          sm.ckpt[q][tid] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+        const uint2* tabRow = sm.tab[buf] + (pb & (TC - 1));
+#pragma unroll 1
+        for (int b = 0; b < nb; b++) {
+          RowGroups<0>::run(w, e0, e1, tabRow + b * BLOCK_ROWS, &sm.ring[0][g]);
+          g = (g + 1 == (uint32_t)NSLOT) ? 0u : g + 1;
+        }
 
-        // post-pass: left-edge band and hit replay
+        // post-pass: hit replay, and the band left of column 0 in the first tiles
+        const uint32_t rows = (uint32_t)nb * BLOCK_ROWS;
         uint32_t mx = 0;
 #pragma unroll
         for (int k = 0; k < R; k += 2) mx = __vimax3_s16x2(mx, w[k], w[k + 1]);
-        bool needAll = false;
-        if (d0 + (long long)pb < 0) {  // some of my cells in this block lie left of column 0
-          if (d0 + 2 * R - 1 + (long long)pb + BLOCK_ROWS - 1 < 0) {
+        const bool edge = D0 + (long long)pb < 0;  // tile-uniform: diagonals left of column 0 remain
+        if (edge || __any_sync(FULL, has_inf(mx))) {
+          // cold path: hand a copy to the out-of-line replay so w stays in registers above
+          uint32_t wc[R];
 #pragma unroll
-            for (int k = 0; k < R; k++) w[k] = 0u;  // all of them: nothing real yet
-            mx = 0;
-          } else {
-            needAll = true;
-          }
-        }
-        if (__any_sync(FULL, needAll || has_inf(mx))) {
-          // cold path: hand copies to the out-of-line replay so w/sv stay in registers above
-          uint32_t svc[R], wc[R];
-#pragma unroll
-          for (int k = 0; k < R; k++) { svc[k] = sv[k]; wc[k] = w[k]; }
-          exact_block(prm, sm, sm.tab[buf], svc, wc, needAll, d0, D0, pb);
+          for (int k = 0; k < R; k++) wc[k] = w[k];
+          exact_rows(prm, sm, sm.tab[buf], wc, edge, d0, D0, pb, rows);
 #pragma unroll
           for (int k = 0; k < R; k++) w[k] = wc[k];
         }
       }
 
-      __syncthreads();  // all reads of tab[buf] and of the ring tail about to be recycled are done
+      __syncthreads();  // all reads of tab[buf] and of the ring part about to be recycled are done
       if (tid == 0) {
         if (c + 2 < c1) {
           mbar_expect_tx(&sm.mbar[buf], TC * sizeof(uint2));
@@ -418,19 +474,14 @@ __global__ void __launch_bounds__(THREADS, 2) ssv_f16x2_kernel(const SsvParams p
         }
         if (*prm.abortFlag) sm.abortSeen = 1;
       }
-      if (tid < TC / 64 && c + 1 < c1) {
-        uint8_t* dst = sm.ring + ((uint32_t)(jRefill - D0 + 64 * tid) & RING_MASK);
-        reinterpret_cast<uint4*>(dst)[0] = expand16(refill.x);
-        reinterpret_cast<uint4*>(dst)[1] = expand16(refill.y);
-        reinterpret_cast<uint4*>(dst)[2] = expand16(refill.z);
-        reinterpret_cast<uint4*>(dst)[3] = expand16(refill.w);
-      }
+      if (doRefill) ring_fill16(sm, sRefill + 16u * (uint32_t)tid, refill0, refill1);
       if (sm.abortSeen) break;  // uniform: written before the barrier of the previous chunk
     }
     __syncthreads();
     if (sm.abortSeen) break;
   }
   if (tid == 0 && sm.abortSeen) atomicOr(prm.status, SSV_STATUS_ABORTED);
+  if (tid == 0 && blockIdx.x == 0) *prm.smCycles = (unsigned long long)(clock64() - clk0);
 }
 
 }  // namespace
@@ -444,9 +495,22 @@ void ssv_launch_table_prep(const int8_t* tab8, uint32_t nRows, uint2* tab16, uin
                                                                               rowsPadded);
 }
 
+static bool f16x2_prepare() {
+  // the kernel needs more than the 48 KB of shared memory a launch gets by default
+  static int done = -1;  // per process; every device of this process runs the same image
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaError_t e = cudaFuncSetAttribute(ssv_f16x2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem));
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(ssv_f16x2_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  done = (e == cudaSuccess);
+  return done == 1;
+}
+
 int ssv_f16x2_ctas_per_sm() {
   int n = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, ssv_f16x2_kernel, THREADS, 0);
+  f16x2_prepare();
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, ssv_f16x2_kernel, THREADS, sizeof(FastSmem));
   return n > 0 ? n : 1;
 }
 
@@ -454,7 +518,7 @@ void ssv_launch_f16x2(const SsvParams& prm, int numSMs, void* stream) {
   int grid = numSMs * ssv_f16x2_ctas_per_sm();
   if ((unsigned)grid > prm.nTiles) grid = (int)prm.nTiles;
   if (grid < 1) grid = 1;
-  ssv_f16x2_kernel<<<grid, THREADS, 0, (cudaStream_t)stream>>>(prm);
+  ssv_f16x2_kernel<<<grid, THREADS, sizeof(FastSmem), (cudaStream_t)stream>>>(prm);
 }
 
 void ssv_launch_scalar(const SsvParams& prm, void* stream) {

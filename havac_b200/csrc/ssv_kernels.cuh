@@ -29,6 +29,7 @@ struct SsvParams {
   unsigned int* tileCounter;
   const volatile int* abortFlag;  // device memory; non-zero = stop (written by the host on a side stream)
   int* status;                    // bit 0: hit buffer overflow, bit 1: aborted
+  unsigned long long* smCycles;   // SM clock cycles CTA 0 spent in the kernel (effective-clock probe)
 };
 
 enum : int { SSV_STATUS_OVERFLOW = 1, SSV_STATUS_ABORTED = 2 };
@@ -39,6 +40,7 @@ constexpr int SSV_THREADS = 256;
 constexpr int SSV_TILE_DIAGS = SSV_THREADS * 2 * SSV_R;  // 8192
 constexpr int SSV_ROW_CHUNK = 512;   // rows of the score table staged per TMA bulk copy
 constexpr int SSV_BLOCK_ROWS = 2 * SSV_R;
+constexpr int SSV_SUPERBLOCK_BLOCKS = 4;  // 32-row blocks between two hit checks (128 rows)
 
 // host-callable launchers (defined in ssv_kernels.cu); all asynchronous on `stream`.
 void ssv_launch_table_prep(const int8_t* tab8, uint32_t nRows, uint2* tab16, uint32_t rowsPadded,

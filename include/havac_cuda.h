@@ -108,6 +108,9 @@ int havac_cuda_device_count(havac_cuda_client* c, int* n);
 /* Per-run facts for roofline accounting: cells = real cells computed (rows x columns
  * of this client's range, halo and padding excluded); launches = kernels launched. */
 int havac_cuda_run_stats(havac_cuda_client* c, uint64_t* cells, uint32_t* launches);
+/* SM clock cycles the first persistent CTA spent in the last run's kernel (clock64), max over
+ * devices; cycles / device_time gives the SM clock the kernel actually ran at. */
+int havac_cuda_sm_cycles(havac_cuda_client* c, uint64_t* cycles);
 /* Running totals of the bytes this client copied host->device and device->host. */
 int havac_cuda_transfer_stats(havac_cuda_client* c, uint64_t* h2dBytes, uint64_t* d2hBytes);
 /* Select a kernel variant by name ("auto" | "f16x2" | "scalar"); for tests that

@@ -18,7 +18,7 @@ def main():
     for i in range(reps):
         t0 = time.time(); c.invokeHavacSsvAsync(); st = c.waitForHavacSsvAsync(); wall = time.time() - t0
         ms = c.deviceTimeMs()
-        print(f"run {i}: state={st} hits={c.getNumHits()} device={ms:.2f} ms wall={wall*1e3:.1f} ms  GCUPS={n*rows/ms/1e6:.1f}", flush=True)
+        print(f"run {i}: state={st} hits={c.getNumHits()} device={ms:.2f} ms wall={wall*1e3:.1f} ms  GCUPS={n*rows/ms/1e6:.1f} effMHz={c.smCycles()/ms/1e3:.0f}", flush=True)
 
 if __name__ == "__main__":
     main()
