@@ -6,16 +6,18 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 
 #define ITER 4096
 #define CHAINS 16
 
 template <int MODE>
-__global__ void k(uint32_t* out, uint32_t seed, long long* cycles) {
+__global__ void k(uint32_t* out, uint32_t seed, long long* cycles, int reps) {
   uint32_t w[CHAINS], s[CHAINS];
   for (int i = 0; i < CHAINS; i++) { w[i] = seed * (i + 1) + threadIdx.x; s[i] = 0x3210 + ((seed + i) & 0x1111); }
   uint32_t a = seed ^ 0x12345678u, b = seed * 7u;
   long long t0 = clock64();
+  for (int rep = 0; rep < reps; rep++)
   for (int it = 0; it < ITER; it++) {
 #pragma unroll
     for (int i = 0; i < CHAINS; i++) {
@@ -51,6 +53,7 @@ __global__ void k(uint32_t* out, uint32_t seed, long long* cycles) {
   if (threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
 }
 
+static int g_reps = 1;
 template <int MODE>
 void run(const char* name, int instrPerChain, int warpsPerSM) {
   int dev = 0, sms = 0;
@@ -61,22 +64,23 @@ void run(const char* name, int instrPerChain, int warpsPerSM) {
   long long* cyc;
   cudaMalloc(&out, sizeof(uint32_t) * sms * threads);
   cudaMalloc(&cyc, sizeof(long long) * sms);
-  k<MODE><<<sms, threads>>>(out, 12345u, cyc);
+  k<MODE><<<sms, threads>>>(out, 12345u, cyc, g_reps);
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0);
-  k<MODE><<<sms, threads>>>(out, 12345u, cyc);
+  k<MODE><<<sms, threads>>>(out, 12345u, cyc, g_reps);
   cudaEventRecord(e1);
   cudaDeviceSynchronize();
   float ms; cudaEventElapsedTime(&ms, e0, e1);
   long long c0; cudaMemcpy(&c0, cyc, sizeof c0, cudaMemcpyDeviceToHost);
-  double warpInstr = (double)ITER * CHAINS * instrPerChain * warpsPerSM;
+  double warpInstr = (double)g_reps * ITER * CHAINS * instrPerChain * warpsPerSM;
   printf("%-28s warps/SM=%2d  cycles=%9lld  warp-instr/clk/SM=%.3f  (lanes/clk/SM=%.1f)  time=%.3f ms  implied MHz=%.0f\n",
          name, warpsPerSM, c0, warpInstr / c0, 32 * warpInstr / c0, ms, c0 / (ms * 1e3));
   cudaFree(out); cudaFree(cyc);
 }
 
-int main() {
+int main(int argc, char** argv) {
+  if (argc > 1) g_reps = atoi(argv[1]);  // >1: long runs that show the sustained (power-managed) clock
   for (int w : {4, 8, 16, 32}) {
     run<0>("PRMT", 1, w);
     run<1>("HFMA2.RELU", 1, w);

@@ -40,7 +40,15 @@ __global__ void __launch_bounds__(THREADS, 2) core_loop(uint32_t* out, int iters
 #pragma unroll
   for (int k = 0; k < R; k++) acc ^= w[k] ^ e0[k] ^ e1[k];
   out[blockIdx.x * THREADS + tid] = acc;
-  if (tid == 0) cycles[blockIdx.x] = t1 - t0;
+  if (tid == 0) {
+    unsigned long long ns;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    cycles[blockIdx.x] = t1 - t0;
+    cycles[gridDim.x + blockIdx.x] = (long long)ns;      // end time
+    cycles[2 * gridDim.x + blockIdx.x] = (long long)smid;
+  }
 }
 
 template <int MODE>
@@ -53,7 +61,7 @@ void run(const char* name, int ctasPerSM) {
   uint32_t* out;
   long long* cyc;
   cudaMalloc(&out, sizeof(uint32_t) * grid * THREADS);
-  cudaMalloc(&cyc, sizeof(long long) * grid);
+  cudaMalloc(&cyc, sizeof(long long) * grid * 3);
   core_loop<MODE><<<grid, THREADS, sizeof(FastSmem)>>>(out, 100, cyc);
   cudaEvent_t a, b;
   cudaEventCreate(&a); cudaEventCreate(&b);
@@ -65,6 +73,22 @@ void run(const char* name, int ctasPerSM) {
   cudaEventElapsedTime(&ms, a, b);
   long long c0 = 0;
   cudaMemcpy(&c0, cyc, sizeof c0, cudaMemcpyDeviceToHost);
+  {
+    long long* h = new long long[grid * 3];
+    cudaMemcpy(h, cyc, sizeof(long long) * grid * 3, cudaMemcpyDeviceToHost);
+    long long cmin = h[0], cmax = h[0], emin = h[grid], emax = h[grid];
+    int perSm[256] = {0};
+    for (int i = 0; i < grid; i++) {
+      cmin = h[i] < cmin ? h[i] : cmin; cmax = h[i] > cmax ? h[i] : cmax;
+      emin = h[grid + i] < emin ? h[grid + i] : emin; emax = h[grid + i] > emax ? h[grid + i] : emax;
+      perSm[h[2 * grid + i] & 255]++;
+    }
+    int hist[8] = {0};
+    for (int i = 0; i < 256; i++) hist[perSm[i] > 7 ? 7 : perSm[i]]++;
+    printf("    per-CTA cycles min %lld max %lld; end-time spread %.3f ms; SMs by CTA count: 0:%d 1:%d 2:%d 3:%d 4+:%d\n", cmin, cmax,
+           (emax - emin) / 1e6, hist[0], hist[1], hist[2], hist[3], hist[4] + hist[5] + hist[6] + hist[7]);
+    delete[] h;
+  }
   double cells = (double)iters * BLOCK_ROWS * (2.0 * R) * THREADS * ctasPerSM;  // per SM
   printf("%-22s ctas/SM=%d  %s  cycles=%lld  cells/clk/SM=%.1f (%.1f%% of 128)  time=%.2f ms  -> %.1f GCUPS on %d SMs\n", name,
          ctasPerSM, cudaGetErrorString(e), c0, cells / c0, 100.0 * cells / c0 / 128.0, ms, cells * sms / ms / 1e6, sms);
