@@ -59,7 +59,9 @@ def build_host(force: bool = False) -> str:
     deps = cpp + _sources(HOST, (".hpp", ".h")) + _sources(INCLUDE, (".h",))
     if force or _stale(HOST_LIB, deps):
         cxx = os.environ.get("CXX") or shutil.which("g++") or "g++"
-        cmd = [cxx, *CXX_FLAGS, "-I", INCLUDE, "-I", HOST, "-o", HOST_LIB, *cpp, "-ldl", "-lpthread"]
+        # links against the CUDA device client next to it ($ORIGIN), so build that first
+        cmd = [cxx, *CXX_FLAGS, "-I", INCLUDE, "-I", HOST, "-o", HOST_LIB, *cpp, "-L", LIB, "-lhavac_cuda",
+               "-Wl,-rpath,$ORIGIN", "-lpthread"]
         subprocess.run(cmd, check=True)
     return HOST_LIB
 

@@ -1,0 +1,92 @@
+#include "Havac.hpp"
+
+#include <algorithm>
+#include <iostream>
+#include <sstream>
+#include <stdexcept>
+
+Havac::Havac(const uint32_t deviceIndex, const float requiredPValue, const std::string xclbinSrc)
+    : deviceIndex(deviceIndex), requiredPValue(requiredPValue), havacXclbinFileSrc(xclbinSrc) {
+  // opens the device and allocates the hit buffers (host/Havac.cpp:24, HavacHwClient.cpp:24-31);
+  // throws when no sm_100 GPU is present -- there is no host fallback for the search
+  this->hwClient = std::make_shared<HavacHwClient>(this->havacXclbinFileSrc, this->havacKernelName, deviceIndex);
+}
+
+Havac::~Havac() {}
+
+void Havac::loadPhmm(const std::string phmmSrc) {
+  this->models.readP7Hmm(phmmSrc);  // std::runtime_error on a malformed file (host/Havac.cpp:48-50)
+  this->compressedPhmmScores = this->models.projectForThreshold256(this->requiredPValue);
+  this->hwClient->writePhmm(this->compressedPhmmScores);
+  this->phmmLoadedToDevice = true;
+}
+
+void Havac::loadSequence(const std::string fastaSrc) {
+  this->fasta.readFasta(fastaSrc);  // runtime_error / bad_alloc as host/Havac.cpp:59-67
+  this->hwClient->writeSequence(this->fasta.compressedSequenceBuffer());
+  this->sequenceLoadedToDevice = true;
+}
+
+void Havac::runHardwareClient() {
+  this->runHardwareClientAsync();
+  this->waitHardwareClientAsync();
+}
+
+void Havac::runHardwareClientAsync() {
+  if (!this->phmmLoadedToDevice)
+    throw std::logic_error("Phmm was not loaded to device before hardware was requested to run.");
+  if (!this->sequenceLoadedToDevice)
+    throw std::logic_error("Sequence was not loaded to device before hardware was requested to run.");
+  this->hwClient->invokeHavacSsvAsync();
+}
+
+void Havac::waitHardwareClientAsync() { this->hwClient->waitForHavacSsvAsync(); }
+
+void Havac::abortHardwareClient() { this->hwClient->abort(); }
+
+enum havac_cmd_state Havac::currentHardwareState() { return (havac_cmd_state)hwClient->getHwState(); }
+
+float Havac::lastDeviceTimeMs() { return hwClient->deviceTimeMs(); }
+
+vector<HavacHit> havacResolveHits(const vector<uint64_t>& rawHits, const FastaSequences& fasta,
+                                  const vector<uint32_t>& prefixSums) {
+  vector<HavacHit> resolved;
+  resolved.reserve(rawHits.size());
+  for (uint64_t i = 0; i < rawHits.size(); i++) {
+    const uint64_t raw = rawHits[i];
+    const uint64_t cell = raw & ((1ULL << 14) - 1);
+    const uint64_t segment = (raw & ((1ULL << 40) - 1)) >> 14;
+    const uint64_t globalSequencePosition = segment * HAVAC_SEGMENT_SYMBOLS + cell;
+    const uint32_t globalPhmmPosition = (uint32_t)(raw >> 40);
+
+    FastaLocalPosition where;
+    if (!fasta.localPositionFromGlobal(globalSequencePosition, where)) continue;  // a hit in the zero padding
+
+    // last prefix sum <= the global row (phmmPrefixSumsBinarySearch, host/Havac.cpp:119-142)
+    auto it = std::upper_bound(prefixSums.begin(), prefixSums.end(), globalPhmmPosition);
+    if (it == prefixSums.begin()) {
+      std::cerr << "ERROR: could not resolve phmm position for raw hit report #" << i << "\n" << std::endl;
+      continue;
+    }
+    const uint32_t phmmIndex = (uint32_t)(it - prefixSums.begin()) - 1;
+    resolved.push_back(HavacHit(where.positionInSequence, (uint32_t)where.sequenceIndex,
+                                globalPhmmPosition - prefixSums[phmmIndex], phmmIndex));
+  }
+  return resolved;
+}
+
+vector<HavacHit> Havac::getHitsFromFinishedRun() {
+  vector<uint64_t> rawHits = this->hwClient->getHitList();
+  return havacResolveHits(rawHits, this->fasta, this->models.lengthPrefixSums());
+}
+
+HavacHit::HavacHit(const uint64_t sequencePosition, const uint32_t sequenceIndex, const uint32_t phmmPosition,
+                   const uint32_t phmmIndex)
+    : sequencePosition(sequencePosition), sequenceIndex(sequenceIndex), phmmPosition(phmmPosition), phmmIndex(phmmIndex) {}
+
+std::string HavacHit::toString() {
+  std::stringstream out;  // same text as host/Havac.cpp:202-207
+  out << "sequence $" << this->sequenceIndex << ", position " << this->sequencePosition << "; phmm #" << this->phmmIndex
+      << " position " << this->phmmPosition;
+  return out.str();
+}

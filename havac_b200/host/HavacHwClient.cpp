@@ -1,0 +1,98 @@
+// HavacHwClient.cpp -- see HavacHwClient.hpp. Error mapping follows the reference:
+//   length contract broken -> std::length_error   (HavacHwClient.cpp:83-96,112-125,142-147)
+//   call out of order      -> std::logic_error    (HavacHwClient.cpp:168)
+//   device failure         -> std::runtime_error  (HavacHwClient.cpp:179-183)
+//   allocation failure     -> std::bad_alloc
+#include "HavacHwClient.hpp"
+
+#include <cstdio>
+#include <new>
+#include <stdexcept>
+
+HavacHwClient::HavacHwClient(const std::string& xclbinFileSrc, const std::string& havacKernelName, const uint32_t deviceIndex)
+    : kernelName(havacKernelName) {
+  int rc = havac_cuda_create(xclbinFileSrc.c_str(), deviceIndex, &handle);
+  if (rc != HAVAC_CUDA_OK) {
+    std::string msg = havac_cuda_last_error(nullptr);
+    handle = nullptr;
+    if (rc == HAVAC_CUDA_E_NOMEM) throw std::bad_alloc();
+    throw std::runtime_error("could not open the CUDA device client: " + msg);
+  }
+}
+
+HavacHwClient::~HavacHwClient() {
+  if (handle) havac_cuda_destroy(handle);
+}
+
+void HavacHwClient::raise(int code, const char* where) {
+  std::string msg = std::string(where) + ": " + havac_cuda_last_error(handle);
+  switch (code) {
+    case HAVAC_CUDA_E_LENGTH: throw std::length_error(msg);
+    case HAVAC_CUDA_E_LOGIC: throw std::logic_error(msg);
+    case HAVAC_CUDA_E_NOMEM: throw std::bad_alloc();
+    case HAVAC_CUDA_E_INVALID: throw std::invalid_argument(msg);
+    default: throw std::runtime_error(msg);  // E_RUNTIME, E_NODEVICE, E_OVERFLOW
+  }
+}
+
+void HavacHwClient::writeSequence(const std::vector<uint8_t>& compressedSequence) {
+  check(havac_cuda_write_sequence(handle, compressedSequence.data(), compressedSequence.size()), "writeSequence");
+}
+
+void HavacHwClient::writePhmm(std::shared_ptr<std::vector<int8_t>> phmmAsFlattenedArray) {
+  if (!phmmAsFlattenedArray) throw std::invalid_argument("writePhmm: null score table");
+  check(havac_cuda_write_phmm(handle, phmmAsFlattenedArray->data(), phmmAsFlattenedArray->size()), "writePhmm");
+}
+
+void HavacHwClient::invokeHavacSsvAsync() { check(havac_cuda_invoke_async(handle), "invokeHavacSsvAsync"); }
+
+havac_hw_cmd_state HavacHwClient::getHwState() {
+  int st = 0;
+  check(havac_cuda_state(handle, &st), "getHwState");
+  return (havac_hw_cmd_state)st;
+}
+
+havac_hw_cmd_state HavacHwClient::waitForHavacSsvAsync(const std::chrono::milliseconds& timeout) {
+  int st = 0;
+  check(havac_cuda_wait(handle, (uint64_t)timeout.count(), &st), "waitForHavacSsvAsync");
+  return (havac_hw_cmd_state)st;
+}
+
+havac_hw_cmd_state HavacHwClient::abort() {
+  int st = 0;
+  check(havac_cuda_abort(handle, &st), "abort");
+  return (havac_hw_cmd_state)st;
+}
+
+uint32_t HavacHwClient::getNumHits() {
+  uint64_t n = 0;
+  check(havac_cuda_num_hits(handle, &n), "getNumHits");
+  return (uint32_t)n;
+}
+
+std::vector<uint64_t> HavacHwClient::getHitList() {
+  uint64_t n = 0;
+  check(havac_cuda_num_hits(handle, &n), "getHitList");
+  std::printf("client reported %llu hits\n", (unsigned long long)n);  // HavacHwClient.cpp:189
+  std::vector<uint64_t> hits(n);
+  uint64_t got = 0;
+  check(havac_cuda_read_hits(handle, hits.data(), hits.size(), &got), "getHitList");
+  hits.resize(got);
+  return hits;
+}
+
+void HavacHwClient::setSegmentRange(uint64_t segBegin, uint64_t segEnd) {
+  check(havac_cuda_set_segment_range(handle, segBegin, segEnd), "setSegmentRange");
+}
+
+float HavacHwClient::deviceTimeMs() {
+  float ms = 0.f;
+  check(havac_cuda_device_time_ms(handle, &ms), "deviceTimeMs");
+  return ms;
+}
+
+int HavacHwClient::deviceCount() {
+  int n = 0;
+  check(havac_cuda_device_count(handle, &n), "deviceCount");
+  return n;
+}

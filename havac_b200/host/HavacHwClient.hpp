@@ -1,0 +1,61 @@
+// HavacHwClient.hpp -- the device client of the Havac driver, B200 edition.
+//
+// Same class name, method names, argument meaning and exception behaviour as the reference's
+// XRT client (host/HavacHwClient.hpp:21-115 and HavacHwClient.cpp), but every XRT call is
+// replaced by one call into the C-ABI of libhavac_cuda (include/havac_cuda.h). Nothing here
+// computes: it only maps error codes back onto the exception types the reference throws.
+#ifndef HAVAC_HW_CLIENT_HPP
+#define HAVAC_HW_CLIENT_HPP
+
+#include <chrono>
+#include <cstdint>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "havac_cuda.h"
+
+// numeric values of XRT's ert_cmd_state, which the reference returns (HavacHwClient.cpp:163-170)
+enum havac_hw_cmd_state {
+  HAVAC_HW_STATE_NEW = 1,
+  HAVAC_HW_STATE_QUEUED = 2,
+  HAVAC_HW_STATE_RUNNING = 3,
+  HAVAC_HW_STATE_COMPLETED = 4,
+  HAVAC_HW_STATE_ERROR = 5,
+  HAVAC_HW_STATE_ABORT = 6,
+  HAVAC_HW_STATE_SUBMITTED = 7,
+  HAVAC_HW_STATE_TIMEOUT = 8,
+  HAVAC_HW_STATE_NORESPONSE = 9
+};
+
+class HavacHwClient {
+public:
+  // `xclbinFileSrc` no longer names a bitstream: it is handed to the C-ABI as the device spec
+  // ("cuda:all", "cuda:0,1", optional ";hitcap=N"); anything else selects GPU `deviceIndex`.
+  HavacHwClient(const std::string& xclbinFileSrc, const std::string& havacKernelName, const uint32_t deviceIndex = 0);
+  HavacHwClient(HavacHwClient&& hc) = delete;
+  HavacHwClient(HavacHwClient& hc) = delete;
+  ~HavacHwClient();
+
+  void writeSequence(const std::vector<uint8_t>& compressedSequence);
+  void writePhmm(std::shared_ptr<std::vector<int8_t>> phmmAsFlattenedArray);
+  void invokeHavacSsvAsync();
+  havac_hw_cmd_state getHwState();
+  havac_hw_cmd_state waitForHavacSsvAsync(const std::chrono::milliseconds& timeout = std::chrono::milliseconds{0});
+  havac_hw_cmd_state abort();
+  std::vector<uint64_t> getHitList();
+
+  // harness helpers (no reference counterpart)
+  void setSegmentRange(uint64_t segBegin, uint64_t segEnd);
+  float deviceTimeMs();
+  int deviceCount();
+
+protected:
+  havac_cuda_client* handle = nullptr;
+  std::string kernelName;
+  uint32_t getNumHits();
+  [[noreturn]] void raise(int code, const char* where);
+  void check(int code, const char* where) { if (code != HAVAC_CUDA_OK) raise(code, where); }
+};
+
+#endif

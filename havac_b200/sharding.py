@@ -1,0 +1,50 @@
+"""Host-side logic of the one-process-per-GPU launch: how the packed sequence is cut into
+per-rank segment ranges, and how the ranks' raw hit lists are merged.
+
+Every diagonal of the SSV matrix is an independent scan (device/HavacHls.cpp:370-402), so ranks
+exchange nothing while searching: rank r searches segments [lo_r, hi_r) with a left halo of
+rows-1 symbols that the device client adds itself (havac_cuda_set_segment_range). The only
+cross-rank step is gathering the hits, which is a host-side concatenation; no NCCL collective
+is on the data path.
+"""
+from __future__ import annotations
+
+from typing import List, Sequence, Tuple
+
+import numpy as np
+
+SEGMENT_SYMBOLS = 12288  # device/PublicDefines.h:18-22
+
+
+def plan_shards(n_segments: int, world_size: int) -> List[Tuple[int, int]]:
+    """Contiguous, near-equal segment ranges [lo, hi) for ranks 0..world_size-1 (some may be
+    empty when there are fewer segments than ranks)."""
+    if n_segments < 0 or world_size < 1:
+        raise ValueError("n_segments must be >= 0 and world_size >= 1")
+    return [(n_segments * r // world_size, n_segments * (r + 1) // world_size) for r in range(world_size)]
+
+
+def halo_symbols(n_rows: int) -> int:
+    """Symbols a shard needs left of its first column for exact hits: a cell (p, i) depends on
+    (p-k, i-k) down to row 0, and rows never reset between concatenated models
+    (test/softSsv/SoftSsv.cpp:31-62), so the halo is the TOTAL table length minus one."""
+    return max(0, n_rows - 1)
+
+
+def emission_order_key(hits: np.ndarray) -> np.ndarray:
+    """Sort key reproducing the FPGA's emission order: segment, then model row, then cell
+    (device/HavacHls.cpp:131-162 loop nest; hit word layout device/HitReporting.cpp:421-430)."""
+    hits = np.asarray(hits, dtype=np.uint64)
+    cell = hits & np.uint64(0x3FFF)
+    seg = (hits >> np.uint64(14)) & np.uint64(0x3FFFFFF)
+    row = hits >> np.uint64(40)
+    return (seg << np.uint64(38)) | (row << np.uint64(14)) | cell
+
+
+def merge_hits(parts: Sequence[np.ndarray]) -> np.ndarray:
+    """Concatenate the ranks' raw hit lists and put them in emission order."""
+    parts = [np.asarray(p, dtype=np.uint64) for p in parts if len(p)]
+    if not parts:
+        return np.zeros(0, dtype=np.uint64)
+    allhits = np.concatenate(parts)
+    return allhits[np.argsort(emission_order_key(allhits), kind="stable")]
