@@ -43,7 +43,7 @@ for _p in (ROOT, os.path.join(ROOT, "tests")):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
-from havac_b200 import synth  # noqa: E402
+from havac_b200 import sharding, synth  # noqa: E402
 
 METRIC = "SSV GCUPS"
 UNIT = "GCUPS"
@@ -231,7 +231,7 @@ def run_gpu(args, rank, world, local_rank):
     packed, table, n_total, lengths = build_workload(world)
     rows = table.shape[0]
     n_seg = len(packed) * 4 // synth.SEGMENT_SYMBOLS
-    seg_lo, seg_hi = n_seg * rank // world, n_seg * (rank + 1) // world
+    seg_lo, seg_hi = sharding.plan_shards(n_seg, world)[rank]
     my_symbols = min(n_total, seg_hi * synth.SEGMENT_SYMBOLS) - seg_lo * synth.SEGMENT_SYMBOLS  # real ones
     log(f"[rank {rank}] workload built in {time.perf_counter() - t_setup:.1f} s: {n_total} symbols, {rows} rows, "
         f"segments [{seg_lo},{seg_hi})")

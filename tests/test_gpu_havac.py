@@ -1,0 +1,190 @@
+"""End to end through the public driver API on a GPU (`Havac`, mirrored from host/Havac.hpp):
+FASTA + .hmm files in, HavacHit 4-tuples out, against the golden vectors the reference objects
+produced and against the CPU oracle. Also the client-call semantics the reference defines:
+call-order errors, size contracts, states, abort, hit-buffer overflow."""
+import ctypes
+import os
+import time
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from havac_b200 import havac, sharding, synth
+from havac_b200.client import (STATE_ABORT, STATE_COMPLETED, HavacHwClient, HitOverflowError, LogicError)
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def tuples(arrs):
+    sp, si, pp, pi = arrs
+    return sorted(zip(sp.tolist(), si.tolist(), pp.tolist(), pi.tolist()))
+
+
+@pytest.mark.parametrize("name", ["two_models", "three_records"])
+def test_havac_files_to_hits_match_golden(name):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    h = havac.Havac(0, float(g["p_value"]))
+    try:
+        # the record terminators become rand()-chosen bases (SequencePreprocessor.cpp:62-85): seed as the
+        # golden run did, through the same libc
+        ctypes.CDLL(None).srand(int(g["seed"]))
+        h.loadSequence(os.path.join(GOLDEN, name + ".fa"))
+        h.loadPhmm(os.path.join(GOLDEN, name + ".hmm"))
+        h.runHardwareClient()
+        assert h.currentHardwareState() == havac.HAVAC_CMD_STATE_COMPLETED
+        got = tuples(h.getHitArraysFromFinishedRun())
+        hits = h.getHitsFromFinishedRun()
+    finally:
+        h.close()
+    want = sorted(map(tuple, g["res"].tolist()))
+    assert len(want) > 10 and got == want
+    assert hits[0].toString().startswith("sequence $") and "; phmm #" in hits[0].toString()
+
+
+def test_havac_multi_record_multi_model_vs_oracle(tmp_path):
+    lens = [150, 90, 400, 33]
+    models = synth.random_models(61, lens)
+    sym = synth.random_symbols(61, 300_000)
+    synth.plant_homologs(61, sym, models, copies=8, substitution=0.1)
+    fa, hmm = str(tmp_path / "s.fa"), str(tmp_path / "m.hmm")
+    synth.write_fasta(fa, synth.split_records(sym, 5))
+    synth.write_hmm(hmm, models)
+    for p in (0.02, 0.1):
+        h = havac.Havac(0, p)
+        try:
+            ctypes.CDLL(None).srand(5)
+            h.loadSequence(fa)
+            h.loadPhmm(hmm)
+            h.runHardwareClientAsync()
+            h.waitHardwareClientAsync()
+            got = tuples(h.getHitArraysFromFinishedRun())
+        finally:
+            h.close()
+        # the oracle side: the same files through the device-free contract doors with the same
+        # srand() seed give the same packed bytes (terminators are rand()-resolved), then softSsv
+        packed, ends = havac.pack_fasta(fa, seed=5)
+        table, mlens = havac.project_phmm(hmm, p)
+        pos, row = O.soft_ssv(synth.unpack_2bit(packed), table)
+        want = tuples(havac.resolve_hits(O.encode_hits(pos, row), ends, mlens))
+        assert len(want) > 10 and got == want
+
+
+def test_call_order_and_size_contracts():
+    h = havac.Havac(0, 0.02)
+    try:
+        with pytest.raises(LogicError, match="Phmm was not loaded"):
+            h.runHardwareClient()
+        with pytest.raises(LogicError):
+            h.currentHardwareState()  # HavacHwClient.cpp:163-170: no run object yet
+    finally:
+        h.close()
+    c = HavacHwClient("")
+    try:
+        with pytest.raises(ValueError, match="multiple of the sequence segment length"):
+            c.writeSequence(np.zeros(100, dtype=np.uint8))
+        with pytest.raises(ValueError, match="divisible by 4"):
+            c.writePhmm(np.zeros(7, dtype=np.int8))
+        with pytest.raises(ValueError, match="cannot be 0"):
+            c.invokeHavacSsvAsync()
+        with pytest.raises(LogicError):
+            c.getHwState()
+    finally:
+        c.close()
+    with pytest.raises(RuntimeError, match="not present"):
+        HavacHwClient("cuda:97")
+
+
+def test_abort_stops_a_long_run_and_reports_abort():
+    table, _ = synth.consensus_score_table(71, 60_000)
+    packed = synth.random_packed(71, 200_000_000)
+    c = HavacHwClient("")
+    try:
+        c.writeSequence(packed)
+        c.writePhmm(table)
+        c.invokeHavacSsvAsync()
+        time.sleep(0.02)
+        t0 = time.perf_counter()
+        st = c.abort()
+        dt = time.perf_counter() - t0
+        assert st == STATE_ABORT and c.getHwState() == STATE_ABORT
+        assert dt < 0.3, f"abort took {dt:.3f} s; the full run is ~0.5 s"
+        # and the client is usable again afterwards
+        c.setKernel("f16x2")
+        small = synth.random_packed(72, 12288 * 4)
+        c.writeSequence(small)
+        c.invokeHavacSsvAsync()
+        assert c.waitForHavacSsvAsync() == STATE_COMPLETED
+    finally:
+        c.close()
+
+
+def test_hit_buffer_overflow_is_reported_not_silent():
+    g = synth.rng(73, 1)
+    table = g.integers(-10, 70, size=(200, 4)).astype(np.int8)  # positive drift: hits everywhere
+    packed = synth.random_packed(73, 12288 * 8)
+    c = HavacHwClient(";hitcap=1000")
+    try:
+        c.writeSequence(packed)
+        c.writePhmm(table)
+        c.invokeHavacSsvAsync()
+        c.waitForHavacSsvAsync()
+        with pytest.raises(HitOverflowError):
+            c.getHitList()
+    finally:
+        c.close()
+
+
+def test_full_size_properties_c2():
+    """BASELINE configs[1] size (100 Mbp x ~35 k rows), where brute force on the CPU is impossible:
+    (1) every GPU hit replays to a hit at exactly that row on its diagonal (no false positives),
+    (2) a fixed sample of whole diagonals replayed on the CPU has exactly the GPU's hits (bounds
+    false negatives), (3) segment-range shards reproduce the whole run."""
+    import bench
+    packed, table, n, _ = bench.build_workload(1)
+    rows = table.shape[0]
+    c = HavacHwClient("")
+    try:
+        c.writeSequence(packed)
+        c.writePhmm(table)
+        c.invokeHavacSsvAsync()
+        assert c.waitForHavacSsvAsync() == STATE_COMPLETED
+        whole = c.getHitList()
+        n_seg = len(packed) * 4 // 12288
+        parts = []
+        for lo, hi in sharding.plan_shards(n_seg, 3):
+            c.setSegmentRange(lo, hi)
+            c.writeSequence(packed)
+            c.invokeHavacSsvAsync()
+            assert c.waitForHavacSsvAsync() == STATE_COMPLETED
+            parts.append(c.getHitList())
+    finally:
+        c.close()
+    assert len(whole) > 1000
+    assert np.array_equal(sharding.merge_hits(parts), whole)
+    cell, seg, row = whole & np.uint64(0x3fff), (whole >> np.uint64(14)) & np.uint64(0x3ffffff), whole >> np.uint64(40)
+    pos = (seg * np.uint64(12288) + cell).astype(np.int64)
+    row = row.astype(np.int64)
+    diag = pos - row
+    L = O.oracle()
+    flat = np.ascontiguousarray(table).reshape(-1)
+    g = synth.rng(74, 1)
+    buf = np.zeros(4096, dtype=np.uint32)
+    W = rows + 8  # a window of the sequence around one diagonal
+
+    def replay(d):
+        a = max(0, d)  # first column of the diagonal
+        b = min(len(packed) * 4, d + rows)
+        lo = (a // 4) * 4
+        sym = synth.unpack_2bit(packed[lo // 4:(b + 3) // 4])
+        k = L.oracle_replay_diagonal(sym, b - lo, flat, rows, d - lo, buf, len(buf))
+        return set(buf[:k].tolist())
+
+    by_diag = {}
+    for d, r in zip(diag.tolist(), row.tolist()):
+        by_diag.setdefault(d, set()).add(r)
+    for d in g.choice(np.array(sorted(by_diag)), size=min(400, len(by_diag)), replace=False).tolist():
+        assert replay(d) == by_diag[d], f"diagonal {d}"
+    for d in g.integers(-(rows - 1), n, size=300).tolist():
+        assert replay(d) == by_diag.get(d, set()), f"sampled diagonal {d}"
