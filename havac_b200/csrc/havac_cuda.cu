@@ -35,12 +35,14 @@ struct DeviceCtx {
   cudaEvent_t evStart = nullptr, evStop = nullptr;
   // sequence shard
   uint32_t* dSeq = nullptr;
+  size_t seqCap = 0;                   // bytes allocated at dSeq (kept across writes of the same size)
   long long resBegin = 0, resEnd = 0;  // global columns resident in dSeq
   long long colBegin = 0, colEnd = 0;  // global columns whose hits this device reports
   // score table
   int8_t* dTab8 = nullptr;
   uint2* dTab16 = nullptr;
   uint32_t rowsPadded = 0;
+  size_t tabCap = 0;  // bytes allocated at dTab8
   // outputs
   unsigned long long* dHits = nullptr;
   unsigned long long* dHitCount = nullptr;
@@ -131,12 +133,13 @@ bool parse_spec(const char* spec, uint32_t deviceIndex, int nDev, std::vector<in
 }
 
 void free_sequence(DeviceCtx& d) {
-  if (d.dSeq) { cudaSetDevice(d.dev); cudaFree(d.dSeq); d.dSeq = nullptr; }
+  if (d.dSeq) { cudaSetDevice(d.dev); cudaFree(d.dSeq); d.dSeq = nullptr; d.seqCap = 0; }
 }
 void free_table(DeviceCtx& d) {
   cudaSetDevice(d.dev);
   if (d.dTab8) { cudaFree(d.dTab8); d.dTab8 = nullptr; }
   if (d.dTab16) { cudaFree(d.dTab16); d.dTab16 = nullptr; }
+  d.tabCap = 0;
 }
 
 // Pull the per-device results after the stop events have fired; decides the final state.
@@ -166,6 +169,43 @@ int collect(havac_cuda_client* c) {
     c->err = "device hit buffer overflowed (capacity " + std::to_string(c->hitCap) + " hits per device)";
   } else c->finalState = HAVAC_CUDA_STATE_COMPLETED;
   return HAVAC_CUDA_OK;
+}
+
+// The FPGA emits hits by (segment, row, cell) ascending (device/HavacHls.cpp:131-162: outer loop
+// over segments, inner over rows, sieve in cell order); reproduce that order. The key
+// seg<<38 | row<<14 | cell is a bit permutation of the hit word, so the words are turned into
+// keys in place, radix-sorted (11-bit digits, passes whose digit is constant are skipped) and
+// turned back.
+void sort_emission_order(uint64_t* hits, uint64_t n) {
+  if (n < 2) return;
+  auto toKey = [](uint64_t h) { return ((h >> 14) & 0x3ffffffull) << 38 | (h >> 40) << 14 | (h & 0x3fffull); };
+  auto toHit = [](uint64_t k) { return (k & 0x3fffull) | (k >> 38) << 14 | ((k >> 14) & 0xffffffull) << 40; };
+  uint64_t orAll = 0, andAll = ~0ull;
+  for (uint64_t i = 0; i < n; i++) {
+    hits[i] = toKey(hits[i]);
+    orAll |= hits[i];
+    andAll &= hits[i];
+  }
+  if (n < 4096) {
+    std::sort(hits, hits + n);
+  } else {
+    constexpr int BITS = 11, BUCKETS = 1 << BITS;
+    std::vector<uint64_t> tmp(n);
+    uint64_t* src = hits;
+    uint64_t* dst = tmp.data();
+    const uint64_t varying = orAll ^ andAll;  // bits that differ between some two keys
+    for (int shift = 0; shift < 64; shift += BITS) {
+      if (((varying >> shift) & (BUCKETS - 1)) == 0) continue;
+      uint64_t count[BUCKETS] = {0};
+      for (uint64_t i = 0; i < n; i++) count[(src[i] >> shift) & (BUCKETS - 1)]++;
+      uint64_t sum = 0;
+      for (int b = 0; b < BUCKETS; b++) { uint64_t c = count[b]; count[b] = sum; sum += c; }
+      for (uint64_t i = 0; i < n; i++) dst[count[(src[i] >> shift) & (BUCKETS - 1)]++] = src[i];
+      std::swap(src, dst);
+    }
+    if (src != hits) std::memcpy(hits, src, n * sizeof(uint64_t));
+  }
+  for (uint64_t i = 0; i < n; i++) hits[i] = toHit(hits[i]);
 }
 
 }  // namespace
@@ -282,15 +322,18 @@ int havac_cuda_write_sequence(havac_cuda_client* c, const uint8_t* packed, uint6
   const size_t nd = c->devs.size();
   for (size_t i = 0; i < nd; i++) {
     DeviceCtx& d = c->devs[i];
-    free_sequence(d);
     d.colBegin = (long long)((sb + nSeg * i / nd) * SEG);
     d.colEnd = (long long)((sb + nSeg * (i + 1) / nd) * SEG);
     d.resBegin = std::max(0ll, d.colBegin - HALO_RESIDENT) & ~63ll;
     d.resEnd = d.colEnd;
-    if (d.colEnd <= d.colBegin) { d.resBegin = d.resEnd = d.colBegin; continue; }
+    if (d.colEnd <= d.colBegin) { d.resBegin = d.resEnd = d.colBegin; free_sequence(d); continue; }
     size_t bytes = (size_t)(d.resEnd - d.resBegin) / 4;
     CK(cudaSetDevice(d.dev));
-    CK(cudaMalloc(&d.dSeq, bytes));
+    if (bytes != d.seqCap) {  // a reload of the same size (the common case) reuses the allocation
+      free_sequence(d);
+      CK(cudaMalloc(&d.dSeq, bytes));
+      d.seqCap = bytes;
+    }
     CK(cudaMemcpyAsync(d.dSeq, packed + d.resBegin / 4, bytes, cudaMemcpyHostToDevice, d.stream));
     c->h2dBytes += bytes;
   }
@@ -314,12 +357,15 @@ int havac_cuda_write_phmm(havac_cuda_client* c, const int8_t* flat, uint64_t nBy
   if (c->launched && !c->finished) return fail(c, HAVAC_CUDA_E_LOGIC, "a run is in flight");
   c->nRows = (uint32_t)(nBytes / 4);
   for (DeviceCtx& d : c->devs) {
-    free_table(d);
-    if (c->nRows == 0) continue;
-    d.rowsPadded = (c->nRows + SSV_ROW_CHUNK - 1) / SSV_ROW_CHUNK * SSV_ROW_CHUNK;
+    if (c->nRows == 0) { free_table(d); continue; }
     CK(cudaSetDevice(d.dev));
-    CK(cudaMalloc(&d.dTab8, nBytes));
-    CK(cudaMalloc(&d.dTab16, (size_t)d.rowsPadded * sizeof(uint2)));
+    if (nBytes != d.tabCap) {
+      free_table(d);
+      d.rowsPadded = (c->nRows + SSV_ROW_CHUNK - 1) / SSV_ROW_CHUNK * SSV_ROW_CHUNK;
+      CK(cudaMalloc(&d.dTab8, nBytes));
+      CK(cudaMalloc(&d.dTab16, (size_t)d.rowsPadded * sizeof(uint2)));
+      d.tabCap = nBytes;
+    }
     CK(cudaMemcpyAsync(d.dTab8, flat, nBytes, cudaMemcpyHostToDevice, d.stream));
     c->h2dBytes += nBytes;
     ssv_launch_table_prep(d.dTab8, c->nRows, d.dTab16, d.rowsPadded, d.stream);
@@ -474,13 +520,7 @@ int havac_cuda_read_hits(havac_cuda_client* c, uint64_t* out, uint64_t cap, uint
     c->d2hBytes += d.hitCount * sizeof(uint64_t);
     off += d.hitCount;
   }
-  // the FPGA emits hits by (segment, row, cell) ascending (device/HavacHls.cpp:131-162 outer loop
-  // over segments, inner over rows, sieve in cell order); reproduce that order.
-  auto key = [](uint64_t h) {
-    uint64_t cell = h & 0x3fffu, seg = (h >> 14) & 0x3ffffffu, row = h >> 40;
-    return (seg << 38) | (row << 14) | cell;
-  };
-  std::sort(out, out + total, [&](uint64_t a, uint64_t b) { return key(a) < key(b); });
+  sort_emission_order(out, total);
   return HAVAC_CUDA_OK;
 }
 

@@ -21,7 +21,7 @@
 //    p-2), so only one new selector per row per thread is produced.
 //  * Per 2 cells: 1 PRMT (ALU pipe) + 1 HFMA2 (FMA pipe). The kernel is issue-bound, not
 //    memory-bound: per 8192-diagonal row it reads 8 B of table and 1/4 B of sequence.
-//  * Score-table rows are staged into shared memory in 512-row chunks by TMA bulk copies
+//  * Score-table rows are staged into shared memory in 2048-row chunks by TMA bulk copies
 //    (cp.async.bulk + mbarrier, double buffered). The 2-bit packed sequence is read from HBM
 //    one chunk ahead and expanded into a shared-memory ring of ready-made selector windows
 //    (one 32-bit entry per symbol) that slides along the diagonal band; a thread fetches the
@@ -125,10 +125,10 @@ constexpr int SB_ROWS = SB_BLOCKS * BLOCK_ROWS;
 constexpr int NSLOT = (W + 2 * TC) / 32;            // 32-symbol groups the window ring holds
 static_assert(BLOCK_ROWS == 32 && R == 16, "the ring layout assumes 32 diagonals and 32 rows per thread-block");
 static_assert(TC % SB_ROWS == 0, "row chunk must hold whole superblocks");
-static_assert(TC / 16 <= 32, "chunk refill is done by one warp");
+static_assert(TC / 16 <= THREADS, "chunk refill is done by the first TC/16 threads");
 static_assert((W + 2 * TC) % 32 == 0, "ring must hold whole 32-symbol groups");
 
-// Shared memory of one CTA (dynamic; ~60 KB, two CTAs per SM).
+// Shared memory of one CTA (dynamic; ~96 KB at 2048-row chunks, two CTAs per SM).
 //  ring : selector WINDOWS, one 32-bit entry per symbol. The entry of symbol j is
 //         sel(x_j) | sel(x_j+1) << 8 | ..., sel(x) = 0x10 + 0x22 x; PRMT reads bits [15:0], which
 //         pick the fp16 scores of x_j and x_j+1 out of the 8-byte table row. Symbol offset

@@ -3,6 +3,9 @@ import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from havac_b200 import synth
+from havac_b200 import build as _b
+if os.environ.get('HAVAC_CUDA_LIB'):
+    _b.CUDA_LIB = os.path.abspath(os.environ['HAVAC_CUDA_LIB'])
 from havac_b200.client import HavacHwClient
 
 def main():
