@@ -160,3 +160,50 @@ def soft_ssv_parallel(symbols, table, threads, lib=None, cap=1 << 20):
     with ThreadPoolExecutor(threads) as ex:
         parts = list(ex.map(work, range(threads)))
     return np.concatenate([p for p, _ in parts]), np.concatenate([r for _, r in parts])
+
+
+def replay_diagonal(packed, table, d, buf=None):
+    """Rows at which diagonal d (column - row) of the whole padded buffer scores a hit, replayed on
+    the CPU from row max(0,-d) with a window of the packed sequence (oracle_replay_diagonal,
+    mirroring attemptTraceback of test/hmmerSsvRef/hmmerSsvRef.cpp:504-586)."""
+    L = oracle()
+    flat = np.ascontiguousarray(table, dtype=np.int8).reshape(-1)
+    rows = len(flat) // 4
+    if buf is None:
+        buf = np.zeros(8192, dtype=np.uint32)
+    a = max(0, d)
+    b = min(len(packed) * 4, d + rows)
+    lo = (a // 4) * 4
+    sym = np.zeros((b - lo + 3) // 4 * 4, dtype=np.uint8)
+    src = np.ascontiguousarray(packed[lo // 4:(b + 3) // 4])
+    L.oracle_unpack_2bit(src, len(src) * 4, sym)
+    k = L.oracle_replay_diagonal(sym, b - lo, flat, rows, d - lo, buf, len(buf))
+    return set(buf[:k].tolist())
+
+
+def check_hits_by_replay(packed, table, raw_hits, n_hit_diagonals, n_random_diagonals, seed):
+    """Scalable verification: (1) sampled diagonals that carry GPU hits replay to
+    exactly those hit rows, (2) uniformly sampled diagonals replay to exactly the GPU's hits on
+    them (usually none). Returns the number of diagonals checked."""
+    raw = np.asarray(raw_hits, dtype=np.uint64)
+    rows = np.asarray(table).reshape(-1, 4).shape[0]
+    cell, seg, row = raw & np.uint64(0x3fff), (raw >> np.uint64(14)) & np.uint64(0x3ffffff), raw >> np.uint64(40)
+    pos = (seg * np.uint64(12288) + cell).astype(np.int64)
+    diag = pos - row.astype(np.int64)
+    by_diag = {}
+    for d, r in zip(diag.tolist(), row.tolist()):
+        by_diag.setdefault(d, set()).add(int(r))
+    g = np.random.Generator(np.random.PCG64(seed))
+    buf = np.zeros(1 << 16, dtype=np.uint32)
+    checked = 0
+    if by_diag:
+        keys = np.array(sorted(by_diag))
+        for d in g.choice(keys, size=min(n_hit_diagonals, len(keys)), replace=False).tolist():
+            got = replay_diagonal(packed, table, d, buf)
+            assert got == by_diag[d], f"diagonal {d}: GPU rows {sorted(by_diag[d])[:8]} vs replay {sorted(got)[:8]}"
+            checked += 1
+    for d in g.integers(-(rows - 1), len(packed) * 4, size=n_random_diagonals).tolist():
+        got = replay_diagonal(packed, table, d, buf)
+        assert got == by_diag.get(d, set()), f"sampled diagonal {d}"
+        checked += 1
+    return checked
