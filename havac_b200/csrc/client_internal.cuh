@@ -1,0 +1,76 @@
+// client_internal.cuh -- private state of the C-ABI device client, shared by its translation
+// units (havac_cuda.cu: buffers / launch / state; fasta_ingest.cu: FASTA text -> packed sequence).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/havac_cuda.h"
+
+constexpr long long SEG = HAVAC_CUDA_SEGMENT_SYMBOLS;
+constexpr unsigned long long MAX_ROWS = 1ull << 24;  // phmmPos_t is 24 bits (device/HavacHls.hpp:19)
+constexpr long long HALO_RESIDENT = 1ll << 24;       // symbols kept left of a shard (>= MAX_ROWS - 1)
+
+enum KernelKind { KERNEL_AUTO = 0, KERNEL_F16X2 = 1, KERNEL_SCALAR = 2 };
+
+struct DeviceCtx {
+  int dev = 0;
+  int numSMs = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t evStart = nullptr, evStop = nullptr;
+  // sequence shard
+  uint32_t* dSeq = nullptr;
+  size_t seqCap = 0;                   // bytes allocated at dSeq (kept across writes of the same size)
+  long long resBegin = 0, resEnd = 0;  // global columns resident in dSeq
+  long long colBegin = 0, colEnd = 0;  // global columns whose hits this device reports
+  // score table
+  int8_t* dTab8 = nullptr;
+  uint2* dTab16 = nullptr;
+  uint32_t rowsPadded = 0;
+  size_t tabCap = 0;  // bytes allocated at dTab8
+  // outputs
+  unsigned long long* dHits = nullptr;
+  unsigned long long* dHitCount = nullptr;
+  unsigned int* dTileCounter = nullptr;
+  int* dStatus = nullptr;
+  unsigned long long* dCycles = nullptr;  // SM cycles of CTA 0 in the last run
+  unsigned long long cycles = 0;
+  int* dAbort = nullptr;          // device-resident abort flag the kernels poll (L2 hit, no PCIe)
+  cudaStream_t ctlStream = nullptr;  // carries the abort write while the run stream is busy
+  // results of the last finished run
+  unsigned long long hitCount = 0;
+  int status = 0;
+};
+
+struct havac_cuda_client {
+  std::vector<DeviceCtx> devs;
+  std::string err;
+  unsigned long long hitCap = 16ull << 20;  // per device
+  uint64_t segBegin = 0, segEnd = 0;        // 0,0 = whole buffer
+  uint64_t seqSegments = 0;                 // segments in the buffer given to write_sequence
+  uint32_t nRows = 0;
+  bool launched = false, finished = false, aborted = false;
+  int finalState = HAVAC_CUDA_STATE_NEW;
+  int* hostOne = nullptr;    // pinned source word for the asynchronous abort write
+  int kernel = KERNEL_AUTO;
+  uint32_t launches = 0;
+  float lastMs = 0.f;
+  uint64_t h2dBytes = 0, d2hBytes = 0;  // running totals of what crossed PCIe
+  // record table of the last havac_cuda_ingest_fasta
+  std::vector<uint64_t> ingestEnd, ingestHeaderByte;
+};
+
+#define CK(call)                                                                         \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) {                                                             \
+      c->err = std::string(#call) + ": " + cudaGetErrorString(e_);                       \
+      return e_ == cudaErrorMemoryAllocation ? HAVAC_CUDA_E_NOMEM : HAVAC_CUDA_E_RUNTIME; \
+    }                                                                                    \
+  } while (0)
+
+// sets the client's (or, for c == nullptr, this thread's create-time) error text; returns `code`
+int havac_fail(havac_cuda_client* c, int code, const std::string& msg);
+void havac_free_sequence(DeviceCtx& d);

@@ -15,82 +15,24 @@
 #include <thread>
 #include <vector>
 
-#include "../../include/havac_cuda.h"
+#include "client_internal.cuh"
 #include "ssv_kernels.cuh"
 
 namespace {
 
-constexpr long long SEG = HAVAC_CUDA_SEGMENT_SYMBOLS;
-constexpr unsigned long long MAX_ROWS = 1ull << 24;  // phmmPos_t is 24 bits (device/HavacHls.hpp:19)
-constexpr long long HALO_RESIDENT = 1ll << 24;       // symbols kept left of a shard (>= MAX_ROWS - 1)
-
 thread_local std::string g_createError;
-
-enum KernelKind { KERNEL_AUTO = 0, KERNEL_F16X2 = 1, KERNEL_SCALAR = 2 };
-
-struct DeviceCtx {
-  int dev = 0;
-  int numSMs = 0;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t evStart = nullptr, evStop = nullptr;
-  // sequence shard
-  uint32_t* dSeq = nullptr;
-  size_t seqCap = 0;                   // bytes allocated at dSeq (kept across writes of the same size)
-  long long resBegin = 0, resEnd = 0;  // global columns resident in dSeq
-  long long colBegin = 0, colEnd = 0;  // global columns whose hits this device reports
-  // score table
-  int8_t* dTab8 = nullptr;
-  uint2* dTab16 = nullptr;
-  uint32_t rowsPadded = 0;
-  size_t tabCap = 0;  // bytes allocated at dTab8
-  // outputs
-  unsigned long long* dHits = nullptr;
-  unsigned long long* dHitCount = nullptr;
-  unsigned int* dTileCounter = nullptr;
-  int* dStatus = nullptr;
-  unsigned long long* dCycles = nullptr;  // SM cycles of CTA 0 in the last run
-  unsigned long long cycles = 0;
-  int* dAbort = nullptr;          // device-resident abort flag the kernels poll (L2 hit, no PCIe)
-  cudaStream_t ctlStream = nullptr;  // carries the abort write while the run stream is busy
-  // results of the last finished run
-  unsigned long long hitCount = 0;
-  int status = 0;
-};
 
 }  // namespace
 
-struct havac_cuda_client {
-  std::vector<DeviceCtx> devs;
-  std::string err;
-  unsigned long long hitCap = 16ull << 20;  // per device
-  uint64_t segBegin = 0, segEnd = 0;        // 0,0 = whole buffer
-  uint64_t seqSegments = 0;                 // segments in the buffer given to write_sequence
-  uint32_t nRows = 0;
-  bool launched = false, finished = false, aborted = false;
-  int finalState = HAVAC_CUDA_STATE_NEW;
-  int* hostOne = nullptr;    // pinned source word for the asynchronous abort write
-  int kernel = KERNEL_AUTO;
-  uint32_t launches = 0;
-  float lastMs = 0.f;
-  uint64_t h2dBytes = 0, d2hBytes = 0;  // running totals of what crossed PCIe
-};
-
-namespace {
-
-#define CK(call)                                                                         \
-  do {                                                                                   \
-    cudaError_t e_ = (call);                                                             \
-    if (e_ != cudaSuccess) {                                                             \
-      c->err = std::string(#call) + ": " + cudaGetErrorString(e_);                       \
-      return e_ == cudaErrorMemoryAllocation ? HAVAC_CUDA_E_NOMEM : HAVAC_CUDA_E_RUNTIME; \
-    }                                                                                    \
-  } while (0)
-
-int fail(havac_cuda_client* c, int code, const std::string& msg) {
+int havac_fail(havac_cuda_client* c, int code, const std::string& msg) {
   if (c) c->err = msg;
   else g_createError = msg;
   return code;
 }
+
+namespace {
+
+inline int fail(havac_cuda_client* c, int code, const std::string& msg) { return havac_fail(c, code, msg); }
 
 bool parse_spec(const char* spec, uint32_t deviceIndex, int nDev, std::vector<int>& out,
                 unsigned long long& hitCap, std::string& err) {
@@ -132,9 +74,7 @@ bool parse_spec(const char* spec, uint32_t deviceIndex, int nDev, std::vector<in
   return !out.empty();
 }
 
-void free_sequence(DeviceCtx& d) {
-  if (d.dSeq) { cudaSetDevice(d.dev); cudaFree(d.dSeq); d.dSeq = nullptr; d.seqCap = 0; }
-}
+inline void free_sequence(DeviceCtx& d) { havac_free_sequence(d); }
 void free_table(DeviceCtx& d) {
   cudaSetDevice(d.dev);
   if (d.dTab8) { cudaFree(d.dTab8); d.dTab8 = nullptr; }
@@ -209,6 +149,10 @@ void sort_emission_order(uint64_t* hits, uint64_t n) {
 }
 
 }  // namespace
+
+void havac_free_sequence(DeviceCtx& d) {
+  if (d.dSeq) { cudaSetDevice(d.dev); cudaFree(d.dSeq); d.dSeq = nullptr; d.seqCap = 0; }
+}
 
 extern "C" {
 

@@ -31,7 +31,8 @@ EXPORTS = [
     "havac_host_create", "havac_host_destroy", "havac_host_load_sequence", "havac_host_load_phmm", "havac_host_run",
     "havac_host_run_async", "havac_host_wait", "havac_host_abort", "havac_host_state", "havac_host_get_hits",
     "havac_host_device_time_ms", "havac_host_last_error", "havac_host_pack_fasta", "havac_host_project_phmm",
-    "havac_host_scale_factor", "havac_host_resolve_hits",
+    "havac_host_scale_factor", "havac_host_resolve_hits", "havac_host_srand", "havac_host_sequence_table",
+    "havac_host_read_sequence",
 ]
 
 _lib = None
@@ -53,6 +54,10 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
         getattr(L, name).argtypes = [vp, C.c_char_p]
     for name in ("havac_host_run", "havac_host_run_async", "havac_host_wait", "havac_host_abort"):
         getattr(L, name).argtypes = [vp]
+    L.havac_host_srand.argtypes = [C.c_uint]
+    L.havac_host_srand.restype = None
+    L.havac_host_sequence_table.argtypes = [vp, vp, u64, C.POINTER(u64)]
+    L.havac_host_read_sequence.argtypes = [vp, vp, u64, C.POINTER(u64)]
     L.havac_host_state.argtypes = [vp, C.POINTER(C.c_int)]
     L.havac_host_get_hits.argtypes = [vp, vp, vp, vp, vp, u64, C.POINTER(u64)]
     L.havac_host_device_time_ms.argtypes = [vp, C.POINTER(C.c_float)]
@@ -144,6 +149,22 @@ class Havac:
                                                  pi.ctypes.data, n.value, C.byref(n)))
         return sp, si, pp, pi
 
+    def sequenceEndPositions(self) -> np.ndarray:
+        """FastaVector's sequenceEndPosition per loaded record (harness door)."""
+        n = C.c_uint64(0)
+        self._ck(self._L.havac_host_sequence_table(self._h, None, 0, C.byref(n)))
+        ends = np.zeros(n.value, dtype=np.uint64)
+        self._ck(self._L.havac_host_sequence_table(self._h, ends.ctypes.data, len(ends), C.byref(n)))
+        return ends
+
+    def devicePackedSequence(self) -> np.ndarray:
+        """The 2-bit packed sequence as the device holds it, copied back (harness door)."""
+        n = C.c_uint64(0)
+        self._ck(self._L.havac_host_read_sequence(self._h, None, 0, C.byref(n)))
+        buf = np.zeros(n.value, dtype=np.uint8)
+        self._ck(self._L.havac_host_read_sequence(self._h, buf.ctypes.data, buf.nbytes, C.byref(n)))
+        return buf
+
     def lastDeviceTimeMs(self) -> float:
         ms = C.c_float(0)
         self._ck(self._L.havac_host_device_time_ms(self._h, C.byref(ms)))
@@ -159,6 +180,11 @@ class Havac:
             self.close()
         except Exception:
             pass
+
+
+def srand(seed: int) -> None:
+    """Seed the C library's rand() of the host driver (it resolves non-ACGT symbols)."""
+    load_library().havac_host_srand(seed)
 
 
 # ---- device-free contracts ---------------------------------------------------------------------

@@ -130,6 +130,15 @@ bool FastaSequences::localPositionFromGlobal(uint64_t globalPosition, FastaLocal
   return true;
 }
 
+void FastaSequences::adoptDeviceIngest(const std::vector<uint64_t>& sequenceEndPositions, std::vector<std::string> recordHeaders) {
+  ends = sequenceEndPositions;
+  names = std::move(recordHeaders);
+  names.resize(ends.size());
+  nSymbols = symbolCount();
+  packed.clear();
+  deviceOnly = true;
+}
+
 FastaSequences FastaSequences::fromEndPositions(const std::vector<uint64_t>& sequenceEndPositions) {
   FastaSequences f;
   f.ends = sequenceEndPositions;

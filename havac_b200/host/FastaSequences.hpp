@@ -45,6 +45,11 @@ public:
   // that record. Binary search instead of the reference's linear scan; same answers.
   bool localPositionFromGlobal(uint64_t globalPosition, FastaLocalPosition& out) const;
 
+  // Record table of a FASTA that was parsed and packed on the device (HavacHwClient::ingestFasta):
+  // the packed buffer stays in device memory, so compressedSequenceBuffer() is empty afterwards.
+  void adoptDeviceIngest(const std::vector<uint64_t>& sequenceEndPositions, std::vector<std::string> recordHeaders);
+  bool packedOnDeviceOnly() const { return deviceOnly; }
+
   // A record table without sequence data (for resolving hits of a search whose FASTA was read elsewhere).
   static FastaSequences fromEndPositions(const std::vector<uint64_t>& sequenceEndPositions);
 
@@ -53,6 +58,7 @@ private:
   std::vector<std::string> names;
   std::vector<uint8_t> packed;
   uint64_t nSymbols = 0;  // symbols written so far (terminators included)
+  bool deviceOnly = false;
   void pushSymbol(unsigned char c);
   void finishPadding();
 };

@@ -1,6 +1,12 @@
 #include "Havac.hpp"
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include <algorithm>
+#include <cstdlib>
 #include <iostream>
 #include <sstream>
 #include <stdexcept>
@@ -21,9 +27,67 @@ void Havac::loadPhmm(const std::string phmmSrc) {
   this->phmmLoadedToDevice = true;
 }
 
+namespace {
+
+// The whole file, mapped read-only (the text is only read once, by the staging copy to the device).
+struct MappedFile {
+  const uint8_t* data = nullptr;
+  size_t size = 0;
+  int fd = -1;
+  explicit MappedFile(const std::string& path) {
+    fd = ::open(path.c_str(), O_RDONLY);
+    if (fd < 0) throw std::runtime_error("Could not open fasta file for reading.");
+    struct stat st;
+    if (::fstat(fd, &st) != 0) { ::close(fd); throw std::runtime_error("Could not open fasta file for reading."); }
+    size = (size_t)st.st_size;
+    if (size) {
+      void* p = ::mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0);
+      if (p == MAP_FAILED) { ::close(fd); throw std::runtime_error("Error while reading from the opened fasta file."); }
+      ::madvise(p, size, MADV_SEQUENTIAL);
+      data = (const uint8_t*)p;
+    }
+  }
+  ~MappedFile() {
+    if (data) ::munmap((void*)data, size);
+    if (fd >= 0) ::close(fd);
+  }
+};
+
+uint8_t resolveSymbol(void*, unsigned char c) { return havacCompressedSymbol(c); }
+
+// header text of the record whose '>' sits at `at` (FastaVector.c:88-112: up to ';' or newline,
+// keeping printable characters and tabs)
+std::string headerAt(const MappedFile& f, uint64_t at) {
+  std::string h;
+  for (uint64_t i = at + 1; i < f.size; i++) {
+    const unsigned char c = f.data[i];
+    if (c == ';' || c == '\n') break;
+    if ((c >= ' ' && c < 0x80) || c == '\t') h.push_back((char)c);
+  }
+  return h;
+}
+
+}  // namespace
+
 void Havac::loadSequence(const std::string fastaSrc) {
-  this->fasta.readFasta(fastaSrc);  // runtime_error / bad_alloc as host/Havac.cpp:59-67
-  this->hwClient->writeSequence(this->fasta.compressedSequenceBuffer());
+  // First load: the file is parsed and packed on the GPU. A second load appends
+  // to the records already held, as the reference's FastaVector does; that rare case, and
+  // HAVAC_HOST_FASTA=1, take the host reader, which produces the same bytes.
+  const char* forceHost = std::getenv("HAVAC_HOST_FASTA");
+  if (this->fasta.numSequences() == 0 && !(forceHost && forceHost[0] == '1')) {
+    MappedFile file(fastaSrc);
+    std::vector<uint64_t> ends, headerAtByte;
+    this->hwClient->ingestFasta(file.data, file.size, resolveSymbol, nullptr, ends, headerAtByte);
+    std::vector<std::string> headers;
+    headers.reserve(ends.size());
+    for (uint64_t at : headerAtByte) headers.push_back(headerAt(file, at));
+    this->fasta.adoptDeviceIngest(ends, std::move(headers));
+  } else {
+    if (this->fasta.packedOnDeviceOnly())
+      throw std::logic_error("loadSequence: appending to a sequence that was packed on the device needs HAVAC_HOST_FASTA=1 from the first load on");
+    this->fasta.readFasta(fastaSrc);  // runtime_error / bad_alloc as host/Havac.cpp:59-67
+    this->hwClient->writeSequence(this->fasta.compressedSequenceBuffer());
+  }
   this->sequenceLoadedToDevice = true;
 }
 

@@ -60,6 +60,7 @@ public:
 
   // additions for harnesses (no reference counterpart)
   float lastDeviceTimeMs();
+  std::vector<uint8_t> devicePackedSequence() { return hwClient->readSequence(); }  // what the device holds, copied back
   const FastaSequences& sequences() const { return fasta; }
   const PhmmModels& phmms() const { return models; }
 

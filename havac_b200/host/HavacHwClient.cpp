@@ -81,6 +81,24 @@ std::vector<uint64_t> HavacHwClient::getHitList() {
   return hits;
 }
 
+void HavacHwClient::ingestFasta(const uint8_t* text, uint64_t nBytes, uint8_t (*resolve)(void*, unsigned char), void* user,
+                                std::vector<uint64_t>& sequenceEndPositions, std::vector<uint64_t>& headerByteOffsets) {
+  uint64_t nSymbols = 0, nRecords = 0;
+  check(havac_cuda_ingest_fasta(handle, text, nBytes, resolve, user, &nSymbols, &nRecords), "ingestFasta");
+  sequenceEndPositions.assign(nRecords, 0);
+  headerByteOffsets.assign(nRecords, 0);
+  uint64_t n = 0;
+  check(havac_cuda_ingest_records(handle, sequenceEndPositions.data(), headerByteOffsets.data(), nRecords, &n), "ingestFasta");
+}
+
+std::vector<uint8_t> HavacHwClient::readSequence() {
+  uint64_t n = 0;
+  check(havac_cuda_read_sequence(handle, nullptr, 0, &n), "readSequence");
+  std::vector<uint8_t> out(n);
+  check(havac_cuda_read_sequence(handle, out.data(), out.size(), &n), "readSequence");
+  return out;
+}
+
 void HavacHwClient::setSegmentRange(uint64_t segBegin, uint64_t segEnd) {
   check(havac_cuda_set_segment_range(handle, segBegin, segEnd), "setSegmentRange");
 }

@@ -45,6 +45,13 @@ public:
   havac_hw_cmd_state abort();
   std::vector<uint64_t> getHitList();
 
+  // FASTA text -> packed sequence on the device (include/havac_cuda.h: havac_cuda_ingest_fasta);
+  // stands for FastaVector + SequencePreprocessor + writeSequence. `resolve` is asked, in sequence
+  // order, for every symbol that is not A/C/G/T and for every record terminator (c == 0).
+  void ingestFasta(const uint8_t* text, uint64_t nBytes, uint8_t (*resolve)(void*, unsigned char), void* user,
+                   std::vector<uint64_t>& sequenceEndPositions, std::vector<uint64_t>& headerByteOffsets);
+  std::vector<uint8_t> readSequence();
+
   // harness helpers (no reference counterpart)
   void setSegmentRange(uint64_t segBegin, uint64_t segEnd);
   float deviceTimeMs();

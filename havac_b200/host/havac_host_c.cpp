@@ -58,6 +58,26 @@ int havac_host_load_sequence(havac_host* h, const char* fastaSrc) {
   return guarded(h, [&] { h->havac->loadSequence(fastaSrc); });
 }
 
+void havac_host_srand(unsigned seed) { srand(seed); }
+
+int havac_host_sequence_table(havac_host* h, uint64_t* sequenceEnd, uint64_t cap, uint64_t* n) {
+  if (!h || !n) return -1;
+  return guarded(h, [&] {
+    const std::vector<uint64_t>& e = h->havac->sequences().sequenceEndPositions();
+    *n = e.size();
+    if (sequenceEnd && cap >= e.size()) std::copy(e.begin(), e.end(), sequenceEnd);
+  });
+}
+
+int havac_host_read_sequence(havac_host* h, uint8_t* packed, uint64_t cap, uint64_t* n) {
+  if (!h || !n) return -1;
+  return guarded(h, [&] {
+    std::vector<uint8_t> buf = h->havac->devicePackedSequence();
+    *n = buf.size();
+    if (packed && cap >= buf.size()) std::copy(buf.begin(), buf.end(), packed);
+  });
+}
+
 int havac_host_load_phmm(havac_host* h, const char* phmmSrc) {
   if (!h || !phmmSrc) return -1;
   return guarded(h, [&] { h->havac->loadPhmm(phmmSrc); });

@@ -100,6 +100,25 @@ int havac_cuda_abort(havac_cuda_client* c, int* state);
 int havac_cuda_num_hits(havac_cuda_client* c, uint64_t* n);
 int havac_cuda_read_hits(havac_cuda_client* c, uint64_t* out, uint64_t cap, uint64_t* n);
 
+/* FASTA text -> device-resident packed sequence, parsed and packed ON THE DEVICE. For a client
+ * that holds no sequence yet this stands for fastaVectorReadFasta (FastaVector/src/FastaVector.c:
+ * 54-168) + SequencePreprocessor (host/sequence/SequencePreprocessor.cpp:9-85) + writeSequence
+ * (host/HavacHwClient.cpp:78-110) in one call, with bit-identical symbols, record end offsets
+ * and padding. `text` is the whole file in host memory. Symbols that are not A/C/G/T, and the
+ * terminator of every record, are chosen with rand() by the reference (SequencePreprocessor.cpp:
+ * 62-85); `resolve(user, c)` is called once for each of them IN SEQUENCE ORDER (c == 0 for a
+ * terminator) and returns the 2-bit symbol, so the caller keeps that state. E_RUNTIME when the
+ * text has no '>' header before its first sequence line, E_LENGTH at >= 4 GiB packed. */
+typedef uint8_t (*havac_cuda_symbol_fn)(void* user, unsigned char c);
+int havac_cuda_ingest_fasta(havac_cuda_client* c, const uint8_t* text, uint64_t nBytes, havac_cuda_symbol_fn resolve,
+                            void* user, uint64_t* nSymbols, uint64_t* nRecords);
+/* Record table of the last ingest: FastaVector's sequenceEndPosition per record (terminators
+ * counted) and the byte offset of each record's '>' in the text. Call with cap = 0 to learn *n. */
+int havac_cuda_ingest_records(havac_cuda_client* c, uint64_t* sequenceEnd, uint64_t* headerByteOffset, uint64_t cap,
+                              uint64_t* n);
+/* The packed sequence resident on a single-device client, copied back (parity checks). */
+int havac_cuda_read_sequence(havac_cuda_client* c, uint8_t* packedOut, uint64_t capBytes, uint64_t* nBytes);
+
 /* Harness helpers (no reference counterpart). */
 const char* havac_cuda_last_error(havac_cuda_client* c); /* c may be NULL: last create error */
 int havac_cuda_device_time_ms(havac_cuda_client* c, float* ms); /* CUDA-event time of the last

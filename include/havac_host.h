@@ -25,6 +25,12 @@ void havac_host_destroy(havac_host* h);
 /* Havac::loadSequence / loadPhmm                            host/Havac.cpp:42-77 */
 int havac_host_load_sequence(havac_host* h, const char* fastaSrc);
 int havac_host_load_phmm(havac_host* h, const char* phmmSrc);
+/* Harness doors around loadSequence: seed rand() (non-ACGT symbols and record terminators are
+ * rand()-chosen, SequencePreprocessor.cpp:62-85), the record end offsets the driver holds, and the
+ * packed buffer as the DEVICE holds it (copied back), to check the device-side FASTA ingest. */
+void havac_host_srand(unsigned seed);
+int havac_host_sequence_table(havac_host* h, uint64_t* sequenceEnd, uint64_t cap, uint64_t* n);
+int havac_host_read_sequence(havac_host* h, uint8_t* packed, uint64_t cap, uint64_t* n);
 /* Havac::runHardwareClient / Async / wait / abort / state   host/Havac.cpp:80-102,190-192 */
 int havac_host_run(havac_host* h);
 int havac_host_run_async(havac_host* h);

@@ -1,0 +1,188 @@
+"""Device-side FASTA ingest (havac_b200/csrc/fasta_ingest.cu) against the
+reference's own reader. `Havac.loadSequence` parses and packs the file on the GPU; the packed
+buffer is copied back from the device and must equal, byte for byte, what
+fastaVectorReadFasta + SequencePreprocessor produce (committed golden vectors made by the
+reference objects; the reference objects themselves where oracle/_ref is present; and the host
+reader of havac_b200/host/FastaSequences.cpp, which the CPU suite pins to the reference).
+rand() decides non-ACGT symbols and record terminators, so both sides are seeded alike."""
+import json
+import os
+import time
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from havac_b200 import havac, synth
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+GOLDEN = os.path.join(HERE, "golden")
+
+
+def device_ingest(path, seed):
+    h = havac.Havac(0, 0.02)
+    try:
+        havac.srand(seed)
+        h.loadSequence(str(path))
+        return h.devicePackedSequence(), h.sequenceEndPositions()
+    finally:
+        h.close()
+
+
+@pytest.mark.parametrize("name", ["two_models", "three_records"])
+def test_ingest_matches_golden(name):
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    packed, ends = device_ingest(os.path.join(GOLDEN, name + ".fa"), int(z["seed"]))
+    assert np.array_equal(ends, z["seq_end"])
+    assert np.array_equal(packed, z["packed"])
+
+
+def odd_fasta(seed):
+    g = synth.rng(seed, 1)
+    body = bytearray()
+    alphabet = b"ACGTacgtNnRYSWKMryswkmBDHVX*-> \t\x01\x7f\x80\xff"
+    for rec in range(9):
+        body += b">rec%d description\twith tab;and a comment\n" % rec
+        for _ in range(int(g.integers(1, 60))):
+            n = int(g.integers(0, 200))
+            line = bytes(alphabet[i] for i in g.integers(0, len(alphabet), size=n))
+            body += line + (b"\r\n" if g.random() < 0.2 else b"\n")
+            r = g.random()
+            if r < 0.1:
+                body += b";comment line > with a bracket\n"
+            elif r < 0.15:
+                body += b"\n\n"
+            elif r < 0.2:
+                body += b"ACGT;trailing comment ACGT\n"
+    body += b">empty\n>tail\nACGT"  # an empty record, and no newline at end of file
+    return bytes(body)
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_ingest_odd_input_vs_host_reader_and_reference(tmp_path, seed):
+    fa = tmp_path / "odd.fa"
+    fa.write_bytes(odd_fasta(seed))
+    packed, ends = device_ingest(fa, 99)
+    hp, he = havac.pack_fasta(str(fa), seed=99)
+    assert np.array_equal(ends, he) and np.array_equal(packed, hp)
+    if O.ref() is not None:
+        rp, re_, cnt = O.ref_load_fasta(str(fa), seed=99)
+        assert np.array_equal(ends, re_) and np.array_equal(packed, rp)
+
+
+def test_ingest_fuzz_states_across_slices_and_blocks(tmp_path):
+    """Random text over the automaton's alphabet, sized so that every state crosses 64-byte slice
+    and 16 KB block boundaries, including very long lines."""
+    g = synth.rng(55, 1)
+    alphabet = np.frombuffer(b"ACGTNacgtn\n\n>;; \t\r\x00\x90", dtype=np.uint8)
+    weights = np.array([20, 20, 20, 20, 3, 5, 5, 5, 5, 1, 3, 1, 0.5, 0.5, 0.2, 1, 0.5, 0.5, 0.2, 0.2])
+    weights = weights / weights.sum()
+    checked = 0
+    for trial in range(12):
+        n = int(g.integers(100, 200_000))
+        body = g.choice(alphabet, size=n, p=weights).tobytes()
+        if trial % 3 == 0:  # one long line in the middle
+            body = body[: n // 2] + b"\n>long\n" + bytes(g.choice(alphabet[:10], size=70_000)) + body[n // 2:]
+        fa = tmp_path / f"fuzz{trial}.fa"
+        fa.write_bytes(b">first\n" + body if trial % 2 == 0 else body)
+        try:
+            hp, he = havac.pack_fasta(str(fa), seed=7)
+        except RuntimeError:
+            with pytest.raises(RuntimeError):  # sequence before any header: both refuse
+                device_ingest(fa, 7)
+            continue
+        packed, ends = device_ingest(fa, 7)
+        assert np.array_equal(ends, he), f"trial {trial}"
+        assert np.array_equal(packed, hp), f"trial {trial}"
+        checked += 1
+    assert checked >= 6
+
+
+def test_ingest_errors(tmp_path):
+    with pytest.raises(RuntimeError):
+        device_ingest(tmp_path / "missing.fa", 1)
+    bad = tmp_path / "orphan.fa"
+    bad.write_bytes(b"ACGT\n>late\nAC\n")
+    with pytest.raises(RuntimeError):
+        device_ingest(bad, 1)
+    empty = tmp_path / "empty.fa"
+    empty.write_bytes(b"")
+    with pytest.raises(RuntimeError):
+        device_ingest(empty, 1)
+
+
+def test_hits_same_with_device_and_host_ingest(tmp_path, monkeypatch):
+    models = synth.random_models(61, [150, 90])
+    hmm = str(tmp_path / "m.hmm")
+    synth.write_hmm(hmm, models)
+    sym = synth.random_symbols(61, 300_000)
+    synth.plant_homologs(61, sym, models, copies=8, substitution=0.1)
+    fa = str(tmp_path / "s.fa")
+    synth.write_fasta(fa, synth.split_records(sym, 3))
+
+    def hits(force_host):
+        if force_host:
+            monkeypatch.setenv("HAVAC_HOST_FASTA", "1")
+        else:
+            monkeypatch.delenv("HAVAC_HOST_FASTA", raising=False)
+        h = havac.Havac(0, 0.02)
+        try:
+            havac.srand(5)
+            h.loadPhmm(hmm)
+            h.loadSequence(fa)
+            h.runHardwareClient()
+            return sorted(h.getHitsFromFinishedRun())
+        finally:
+            h.close()
+
+    dev, host = hits(False), hits(True)
+    assert len(dev) >= 8 and dev == host
+
+
+def test_ingest_throughput_100mbp(tmp_path, monkeypatch):
+    """Wall time of loadSequence on a 100 Mbp FASTA: device ingest vs the host reader vs (where
+    built) the reference's FastaVector + SequencePreprocessor; appended to gpurun_out."""
+    n = 100_000_000
+    sym = synth.random_symbols(5, n)
+    fa = str(tmp_path / "big.fa")
+    synth.write_fasta(fa, synth.split_records(sym, 4))
+    del sym
+    size = os.path.getsize(fa)
+
+    h = havac.Havac(0, 0.02)
+    try:
+        havac.srand(1)
+        t0 = time.perf_counter()
+        h.loadSequence(fa)
+        t_dev = time.perf_counter() - t0
+        packed, ends = h.devicePackedSequence(), h.sequenceEndPositions()
+    finally:
+        h.close()
+    monkeypatch.setenv("HAVAC_HOST_FASTA", "1")
+    h = havac.Havac(0, 0.02)
+    try:
+        havac.srand(1)
+        t0 = time.perf_counter()
+        h.loadSequence(fa)
+        t_host = time.perf_counter() - t0
+        hp, he = h.devicePackedSequence(), h.sequenceEndPositions()
+    finally:
+        h.close()
+    assert np.array_equal(ends, he) and np.array_equal(packed, hp)
+    line = {"case": "loadSequence 100 Mbp FASTA (4 records, 80 columns)", "file_bytes": size,
+            "device_ingest_s": t_dev, "host_reader_s": t_host, "device_ingest_GBps": size / t_dev / 1e9}
+    if O.ref() is not None:
+        t0 = time.perf_counter()
+        L = O.ref()
+        import ctypes as C
+        ns, cnt = C.c_uint64(0), C.c_uint64(0)
+        L.ref_load_fasta(fa.encode(), 1, None, 0, None, 0, C.byref(ns), C.byref(cnt))  # parse + pack once
+        line["reference_FastaVector_plus_SequencePreprocessor_s"] = time.perf_counter() - t0
+    print(json.dumps(line))
+    out = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, "ingest_bench.jsonl"), "a") as fh:
+            fh.write(json.dumps(line) + "\n")
+    assert t_dev < t_host
