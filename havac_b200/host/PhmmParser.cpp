@@ -16,10 +16,33 @@ namespace {
 
 const char* const FORMAT_ERROR = "Phmm file was not formatted correctly.";
 
-std::vector<char*> splitTokens(char* line) {
-  std::vector<char*> toks;
-  for (char* t = std::strtok(line, " \t\r\n"); t; t = std::strtok(nullptr, " \t\r\n")) toks.push_back(t);
-  return toks;
+inline bool isBlank(char c) { return c == ' ' || c == '\t' || c == '\r' || c == '\n'; }
+
+// Splits `line` in place into whitespace-separated tokens (reusing `toks`' storage: three lines
+// per model position make this the hot loop of a large model database).
+void splitTokens(char* line, std::vector<char*>& toks) {
+  toks.clear();
+  char* p = line;
+  while (true) {
+    while (isBlank(*p)) p++;
+    if (!*p) break;
+    toks.push_back(p);
+    while (*p && !isBlank(*p)) p++;
+    if (!*p) break;
+    *p++ = 0;
+  }
+}
+
+// number of whitespace-separated tokens, without touching the line (insert-emission and
+// transition lines are only checked for their shape: nothing on them reaches the score table)
+size_t countTokens(const char* p) {
+  size_t n = 0;
+  while (true) {
+    while (isBlank(*p)) p++;
+    if (!*p) return n;
+    n++;
+    while (*p && !isBlank(*p)) p++;
+  }
 }
 
 // "%f" of the reference's sscanf: strtof gives the same correctly rounded float. '*' stands for
@@ -60,8 +83,24 @@ void PhmmModels::readP7Hmm(const std::string& phmmSrc) {
 
   auto fail = [&]() -> void { throw std::runtime_error(FORMAT_ERROR); };
 
+  std::vector<char> ioBuffer(1 << 20);
+  std::setvbuf(f, ioBuffer.data(), _IOFBF, ioBuffer.size());
+  std::vector<char*> t;
   while (getline(&line, &cap, f) != -1) {
-    std::vector<char*> t = splitTokens(line);
+    if (state == INSERT_LINE || state == TRANSITION_LINE) {
+      const size_t n = countTokens(line);
+      if (n == 0) continue;  // blank line
+      if (state == INSERT_LINE) {
+        if (n < cur->alphabetCardinality) fail();
+        state = TRANSITION_LINE;
+      } else {
+        if (n < 7) fail();
+        expectedNode++;
+        state = MATCH_LINE;
+      }
+      continue;
+    }
+    splitTokens(line, t);
     if (t.empty()) continue;  // blank line
     switch (state) {
       case IDLE:
@@ -121,8 +160,9 @@ void PhmmModels::readP7Hmm(const std::string& phmmSrc) {
           cur = nullptr;
           break;
         }
-        uint32_t node = 0;
-        if (std::sscanf(t[0], "%u", &node) != 1 || node != expectedNode || node > cur->modelLength) fail();
+        char* endOfNode = nullptr;
+        const unsigned long node = std::strtoul(t[0], &endOfNode, 10);
+        if (endOfNode == t[0] || node != expectedNode || node > cur->modelLength) fail();
         const uint32_t K = cur->alphabetCardinality;
         if (t.size() < 1 + K) fail();
         for (uint32_t a = 0; a < K; a++)
@@ -131,14 +171,8 @@ void PhmmModels::readP7Hmm(const std::string& phmmSrc) {
         break;
       }
       case INSERT_LINE:
-        if (t.size() < cur->alphabetCardinality) fail();
-        state = TRANSITION_LINE;
-        break;
       case TRANSITION_LINE:
-        if (t.size() < 7) fail();
-        expectedNode++;
-        state = MATCH_LINE;
-        break;
+        break;  // handled above, without tokenising
     }
   }
   if (state != IDLE || parsed.empty()) fail();  // truncated model, or no model at all
