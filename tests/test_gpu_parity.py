@@ -147,3 +147,20 @@ def test_hit_order_matches_fpga_emission_order():
     cell, seg, row = hits & np.uint64(0x3fff), (hits >> np.uint64(14)) & np.uint64(0x3ffffff), hits >> np.uint64(40)
     key = (seg << np.uint64(38)) | (row << np.uint64(14)) | cell
     assert len(hits) > 1 and np.all(np.diff(key.astype(np.int64)) > 0)
+
+
+def test_all_gpus_of_the_box_in_one_process():
+    """`cuda:all` shards the sequence over every GPU of the process (halo rows-1 per shard, no
+    exchange); the gathered hits must equal the single-GPU run. Skipped on a one-GPU box."""
+    try:
+        probe = HavacHwClient("cuda:0,1")
+    except RuntimeError:
+        pytest.skip("fewer than two GPUs visible")
+    probe.close()
+    table, cons = consensus_table(41, 700)
+    sym = planted_sequence(41, 40 * synth.SEGMENT_SYMBOLS - 5, cons, copies=60)
+    packed = synth.pack_2bit(sym)
+    one = gpu_hits(packed, table)
+    many = gpu_hits(packed, table, spec="cuda:all")
+    assert len(one) > 20 and np.array_equal(one, many)
+    assert np.array_equal(np.sort(one), oracle_hits(packed, table))
