@@ -400,7 +400,10 @@ __global__ void __launch_bounds__(THREADS, 2) ssv_f16x2_kernel(const SsvParams p
     const uint32_t p0 = (uint32_t)c0 * TC;  // first row; ring holds offsets [p0, p0 + W + 2 TC)
     {
       const long long wFill0 = (D0 + (long long)p0) >> 4;  // D0 and p0 are multiples of 64
-      for (int i = tid; i < (W + 2 * TC) / 16; i += THREADS)
+      // a short table needs only the symbols its rows reach (+ one block of window prefetch)
+      long long need = (long long)W + ((rowEnd - (long long)p0 + 31) & ~31ll) + 64;
+      if (need > W + 2 * TC) need = W + 2 * TC;
+      for (int i = tid; i < (int)(need / 16); i += THREADS)
         ring_fill16(sm, p0 + 16u * (uint32_t)i, load_seq_word(prm, wFill0 + i), load_seq_word(prm, wFill0 + i + 1));
     }
     __syncthreads();
