@@ -23,7 +23,7 @@
 //    memory-bound: per 8192-diagonal row it reads 8 B of table and 1/4 B of sequence.
 //  * Score-table rows are staged into shared memory in 2048-row chunks by TMA bulk copies
 //    (cp.async.bulk + mbarrier, double buffered). The 2-bit packed sequence is read from HBM
-//    one chunk ahead and expanded into a shared-memory ring of ready-made selector windows
+//    with 128-bit accesses (cp.async into a double-buffered staging area, one chunk ahead) and expanded into a shared-memory ring of ready-made selector windows
 //    (one 32-bit entry per symbol) that slides along the diagonal band; a thread fetches the
 //    four windows of four rows with one conflict-free LDS.128, so the hot loop spends no ALU
 //    instruction on selectors.
@@ -125,7 +125,7 @@ constexpr int SB_ROWS = SB_BLOCKS * BLOCK_ROWS;
 constexpr int NSLOT = (W + 2 * TC) / 32;            // 32-symbol groups the window ring holds
 static_assert(BLOCK_ROWS == 32 && R == 16, "the ring layout assumes 32 diagonals and 32 rows per thread-block");
 static_assert(TC % SB_ROWS == 0, "row chunk must hold whole superblocks");
-static_assert(TC / 16 <= THREADS, "chunk refill is done by the first TC/16 threads");
+static_assert(TC % 64 == 0 && TC / 64 <= THREADS, "chunk refill is done by the first TC/64 threads, 64 symbols each");
 static_assert((W + 2 * TC) % 32 == 0, "ring must hold whole 32-symbol groups");
 
 // Shared memory of one CTA (dynamic; ~96 KB at 2048-row chunks, two CTAs per SM).
@@ -136,12 +136,15 @@ static_assert((W + 2 * TC) % 32 == 0, "ring must hold whole 32-symbol groups");
 //         windows a thread needs for four consecutive rows are one LDS.128, and the 32 lanes of a
 //         warp (32 symbols apart) read 32 consecutive uint4 -- conflict-free.
 //  tab  : double-buffered score-table chunks (TMA bulk copies).
+//  seqStage : the packed sequence words that extend the ring for the chunk after next, copied
+//         HBM -> shared memory by cp.async while the current chunk computes (no registers held).
 //  ckpt : the thread's 16 state registers at the start of the current superblock, for the exact
 //         replay (kept in shared memory so the hot loop carries no copies of them).
 struct __align__(16) FastSmem {
   uint4 ring[8][NSLOT];
   uint2 tab[2][TC];
   uint4 ckpt[R / 4][THREADS];
+  uint4 seqStage[2][TC / 64 + 1];  // packed symbols of the chunk after next (cp.async), double buffered
   unsigned long long mbar[2];
   unsigned int nextTile;
   int abortSeen;
@@ -200,6 +203,19 @@ __device__ __forceinline__ uint32_t load_seq_word(const SsvParams& prm, long lon
   return (wi >= 0 && wi < nWords) ? __ldg(prm.seqPacked + wi) : 0u;
 }
 
+// Four packed words (64 symbols) with one 128-bit load; wi is a multiple of 4 and so is the number
+// of resident words, so the vector is either wholly inside the loaded range or wholly outside.
+__device__ __forceinline__ uint4 load_seq_vec(const SsvParams& prm, long long wi) {
+  const long long nWords = prm.nLoad >> 4;
+  if (wi >= 0 && wi + 4 <= nWords) return __ldg(reinterpret_cast<const uint4*>(prm.seqPacked + wi));
+  return make_uint4(0u, 0u, 0u, 0u);
+}
+
+// 16-byte asynchronous copy global -> shared (SASS: LDGSTS); srcBytes = 0 zero-fills instead.
+__device__ __forceinline__ void cp_async16(void* dst, const void* src, uint32_t srcBytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(srcBytes) : "memory");
+}
+
 // Write the 16 window entries of the symbols in packed word `x` (symbol offsets s .. s+15 from
 // the tile's first diagonal, s a multiple of 16); `xNext` is the following packed word, whose
 // first symbol completes the last window.
@@ -218,6 +234,14 @@ __device__ __forceinline__ void ring_fill16(FastSmem& sm, uint32_t s, uint32_t x
     v.w = __funnelshift_r(ow[q], ow[q + 1], 24);
     sm.ring[plane0 + q][slot] = v;
   }
+}
+
+// The same for 64 symbols (one 128-bit vector of the packed sequence plus the word after it).
+__device__ __forceinline__ void ring_fill64(FastSmem& sm, uint32_t s, uint4 v, uint32_t next) {
+  ring_fill16(sm, s, v.x, v.y);
+  ring_fill16(sm, s + 16u, v.y, v.z);
+  ring_fill16(sm, s + 32u, v.z, v.w);
+  ring_fill16(sm, s + 48u, v.w, next);
 }
 
 // PRMT with the raw PTX semantics (CUDA's __byte_perm would first AND the selector with
@@ -401,10 +425,10 @@ __global__ void __launch_bounds__(THREADS, 2) ssv_f16x2_kernel(const SsvParams p
     {
       const long long wFill0 = (D0 + (long long)p0) >> 4;  // D0 and p0 are multiples of 64
       // a short table needs only the symbols its rows reach (+ one block of window prefetch)
-      long long need = (long long)W + ((rowEnd - (long long)p0 + 31) & ~31ll) + 64;
+      long long need = (long long)W + ((rowEnd - (long long)p0 + 63) & ~63ll) + 64;
       if (need > W + 2 * TC) need = W + 2 * TC;
-      for (int i = tid; i < (int)(need / 16); i += THREADS)
-        ring_fill16(sm, p0 + 16u * (uint32_t)i, load_seq_word(prm, wFill0 + i), load_seq_word(prm, wFill0 + i + 1));
+      for (int i = tid; i < (int)(need / 64); i += THREADS)
+        ring_fill64(sm, p0 + 64u * (uint32_t)i, load_seq_vec(prm, wFill0 + 4 * i), load_seq_word(prm, wFill0 + 4 * i + 4));
     }
     __syncthreads();
 
@@ -425,15 +449,16 @@ __global__ void __launch_bounds__(THREADS, 2) ssv_f16x2_kernel(const SsvParams p
     // --- main loop over row chunks -----------------------------------------------------------
     for (int c = c0; c < c1; c++) {
       const int buf = (c - c0) & 1;
-      // prefetch the packed symbols that extend the ring for chunk c+2 (written after compute)
-      uint32_t refill0 = 0, refill1 = 0;
+      // prefetch the packed symbols that extend the ring for chunk c+2: cp.async into shared memory
+      // now, expanded into ring windows after this chunk's compute
       const uint32_t sRefill = (uint32_t)W + (uint32_t)(c + 2) * TC;
-      const bool doRefill = tid < TC / 16 && c + 2 < c1;
-      if (doRefill) {
-        const long long wi = ((D0 + (long long)sRefill) >> 4) + tid;
-        refill0 = load_seq_word(prm, wi);
-        refill1 = load_seq_word(prm, wi + 1);
+      const bool doRefill = c + 2 < c1;
+      if (doRefill && tid <= TC / 64) {  // one vector more than the chunk: the last window needs the word after it
+        const long long wi = ((D0 + (long long)sRefill) >> 4) + 4 * tid;
+        const bool inside = wi >= 0 && wi + 4 <= (prm.nLoad >> 4);
+        cp_async16(&sm.seqStage[buf][tid], prm.seqPacked + (inside ? wi : 0), inside ? 16u : 0u);
       }
+      asm volatile("cp.async.commit_group;" ::: "memory");
       mbar_wait(&sm.mbar[buf], (mbarPhase >> buf) & 1u);
       mbarPhase ^= 1u << buf;
 
@@ -469,7 +494,8 @@ __global__ void __launch_bounds__(THREADS, 2) ssv_f16x2_kernel(const SsvParams p
         }
       }
 
-      __syncthreads();  // all reads of tab[buf] and of the ring part about to be recycled are done
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncthreads();  // all reads of tab[buf] and of the ring part about to be recycled are done; seqStage[buf] landed
       if (tid == 0) {
         if (c + 2 < c1) {
           mbar_expect_tx(&sm.mbar[buf], TC * sizeof(uint2));
@@ -477,7 +503,8 @@ __global__ void __launch_bounds__(THREADS, 2) ssv_f16x2_kernel(const SsvParams p
         }
         if (*prm.abortFlag) sm.abortSeen = 1;
       }
-      if (doRefill) ring_fill16(sm, sRefill + 16u * (uint32_t)tid, refill0, refill1);
+      if (doRefill && tid < TC / 64)
+        ring_fill64(sm, sRefill + 64u * (uint32_t)tid, sm.seqStage[buf][tid], sm.seqStage[buf][tid + 1].x);
       if (sm.abortSeen) break;  // uniform: written before the barrier of the previous chunk
     }
     __syncthreads();
