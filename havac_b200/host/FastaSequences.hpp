@@ -49,6 +49,8 @@ public:
   // the packed buffer stays in device memory, so compressedSequenceBuffer() is empty afterwards.
   void adoptDeviceIngest(const std::vector<uint64_t>& sequenceEndPositions, std::vector<std::string> recordHeaders);
   bool packedOnDeviceOnly() const { return deviceOnly; }
+  // Gives the object its packed buffer back (copied from the device) so that a later readFasta can append.
+  void restorePacked(std::vector<uint8_t> devicePacked) { packed = std::move(devicePacked); deviceOnly = false; }
 
   // A record table without sequence data (for resolving hits of a search whose FASTA was read elsewhere).
   static FastaSequences fromEndPositions(const std::vector<uint64_t>& sequenceEndPositions);

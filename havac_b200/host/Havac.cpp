@@ -71,8 +71,9 @@ std::string headerAt(const MappedFile& f, uint64_t at) {
 
 void Havac::loadSequence(const std::string fastaSrc) {
   // First load: the file is parsed and packed on the GPU. A second load appends
-  // to the records already held, as the reference's FastaVector does; that rare case, and
-  // HAVAC_HOST_FASTA=1, take the host reader, which produces the same bytes.
+  // to the records already held, as the reference's FastaVector does; that rare case (the packed
+  // buffer is first copied back from the device) and HAVAC_HOST_FASTA=1 take the host reader, which
+  // produces the same bytes.
   const char* forceHost = std::getenv("HAVAC_HOST_FASTA");
   if (this->fasta.numSequences() == 0 && !(forceHost && forceHost[0] == '1')) {
     MappedFile file(fastaSrc);
@@ -83,8 +84,8 @@ void Havac::loadSequence(const std::string fastaSrc) {
     for (uint64_t at : headerAtByte) headers.push_back(headerAt(file, at));
     this->fasta.adoptDeviceIngest(ends, std::move(headers));
   } else {
-    if (this->fasta.packedOnDeviceOnly())
-      throw std::logic_error("loadSequence: appending to a sequence that was packed on the device needs HAVAC_HOST_FASTA=1 from the first load on");
+    if (this->fasta.packedOnDeviceOnly())  // appending to a device-packed sequence: take the buffer back first
+      this->fasta.restorePacked(this->hwClient->readSequence());
     this->fasta.readFasta(fastaSrc);  // runtime_error / bad_alloc as host/Havac.cpp:59-67
     this->hwClient->writeSequence(this->fasta.compressedSequenceBuffer());
   }

@@ -186,3 +186,78 @@ def test_ingest_throughput_100mbp(tmp_path, monkeypatch):
         with open(os.path.join(out, "ingest_bench.jsonl"), "a") as fh:
             fh.write(json.dumps(line) + "\n")
     assert t_dev < t_host
+
+
+def test_second_load_appends_like_the_reference(tmp_path, monkeypatch):
+    """FastaVector appends when loadSequence is called twice; after a device-side first load the
+    packed buffer is taken back from the device and the host reader appends to it."""
+    a, b = tmp_path / "a.fa", tmp_path / "b.fa"
+    a.write_bytes(b">a1\nACGTNACGT\n>a2\nGGGTTT\n")
+    b.write_bytes(b">b1\nTTTTNNAC\nCCC\n")
+
+    def both_loads(force_host):
+        if force_host:
+            monkeypatch.setenv("HAVAC_HOST_FASTA", "1")
+        else:
+            monkeypatch.delenv("HAVAC_HOST_FASTA", raising=False)
+        h = havac.Havac(0, 0.02)
+        try:
+            havac.srand(11)
+            h.loadSequence(str(a))
+            h.loadSequence(str(b))
+            return h.devicePackedSequence(), h.sequenceEndPositions()
+        finally:
+            h.close()
+
+    dp, de = both_loads(False)
+    hp, he = both_loads(True)
+    assert np.array_equal(de, he) and len(de) == 3
+    assert np.array_equal(dp, hp)
+
+
+def test_ingest_on_a_multi_gpu_client(tmp_path):
+    """With `cuda:all` the ingest runs on the first device and the shards go out through the
+    ordinary path; hits must equal the single-GPU run."""
+    from havac_b200.client import HavacHwClient
+    try:
+        HavacHwClient("cuda:0,1").close()
+    except RuntimeError:
+        pytest.skip("fewer than two GPUs visible")
+    models = synth.random_models(62, [120, 200])
+    hmm = str(tmp_path / "m.hmm")
+    synth.write_hmm(hmm, models)
+    sym = synth.random_symbols(62, 400_000)
+    synth.plant_homologs(62, sym, models, copies=10, substitution=0.1)
+    fa = str(tmp_path / "s.fa")
+    synth.write_fasta(fa, synth.split_records(sym, 2))
+
+    def hits(spec):
+        h = havac.Havac(0, 0.02, spec)
+        try:
+            havac.srand(5)
+            h.loadPhmm(hmm)
+            h.loadSequence(fa)
+            h.runHardwareClient()
+            return sorted(h.getHitsFromFinishedRun())
+        finally:
+            h.close()
+
+    one, many = hits(""), hits("cuda:all")
+    assert len(one) >= 10 and one == many
+
+
+def test_cpp_user_program_reports_the_golden_hits(tmp_path):
+    """examples/havac_benchmark.cpp (a C++ program against the Havac class) on the golden files."""
+    import subprocess
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "examples"))
+    import run_benchmark
+    exe = run_benchmark.build_program()
+    z = np.load(os.path.join(GOLDEN, "two_models.npz"))
+    out = subprocess.run([exe, "", os.path.join(GOLDEN, "two_models.fa"), os.path.join(GOLDEN, "two_models.hmm"), "0.02"],
+                         check=True, capture_output=True, text=True).stdout
+    line = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
+    assert line["records"] == len(z["seq_end"]) and line["rows"] == int(z["model_len"].sum())
+    # the program seeds rand() with 1, the golden set with its own seed: symbols chosen by rand()
+    # (record terminators here) may differ, hits away from them may not
+    assert abs(line["hits"] - len(z["res"])) <= 2
