@@ -29,7 +29,7 @@ EXPORTS = [
     "havac_cuda_set_segment_range", "havac_cuda_invoke_async", "havac_cuda_state", "havac_cuda_wait",
     "havac_cuda_abort", "havac_cuda_num_hits", "havac_cuda_read_hits", "havac_cuda_last_error",
     "havac_cuda_device_time_ms", "havac_cuda_device_count", "havac_cuda_run_stats", "havac_cuda_set_kernel", "havac_cuda_transfer_stats", "havac_cuda_sm_cycles",
-    "havac_cuda_ingest_fasta", "havac_cuda_ingest_records", "havac_cuda_read_sequence",
+    "havac_cuda_ingest_fasta", "havac_cuda_ingest_records", "havac_cuda_read_sequence", "havac_cuda_resolve_hits",
 ]
 
 

@@ -42,6 +42,7 @@ struct DeviceCtx {
   // results of the last finished run
   unsigned long long hitCount = 0;
   int status = 0;
+  bool hitsSorted = false;  // dHits already put into emission order (hit_postprocess.cu)
 };
 
 struct havac_cuda_client {
@@ -74,3 +75,5 @@ struct havac_cuda_client {
 // sets the client's (or, for c == nullptr, this thread's create-time) error text; returns `code`
 int havac_fail(havac_cuda_client* c, int code, const std::string& msg);
 void havac_free_sequence(DeviceCtx& d);
+// hit_postprocess.cu: sorts d.dHits[0, d.hitCount) into the FPGA's emission order on the device
+int havac_sort_hits_on_device(havac_cuda_client* c, DeviceCtx& d);

@@ -111,43 +111,6 @@ int collect(havac_cuda_client* c) {
   return HAVAC_CUDA_OK;
 }
 
-// The FPGA emits hits by (segment, row, cell) ascending (device/HavacHls.cpp:131-162: outer loop
-// over segments, inner over rows, sieve in cell order); reproduce that order. The key
-// seg<<38 | row<<14 | cell is a bit permutation of the hit word, so the words are turned into
-// keys in place, radix-sorted (11-bit digits, passes whose digit is constant are skipped) and
-// turned back.
-void sort_emission_order(uint64_t* hits, uint64_t n) {
-  if (n < 2) return;
-  auto toKey = [](uint64_t h) { return ((h >> 14) & 0x3ffffffull) << 38 | (h >> 40) << 14 | (h & 0x3fffull); };
-  auto toHit = [](uint64_t k) { return (k & 0x3fffull) | (k >> 38) << 14 | ((k >> 14) & 0xffffffull) << 40; };
-  uint64_t orAll = 0, andAll = ~0ull;
-  for (uint64_t i = 0; i < n; i++) {
-    hits[i] = toKey(hits[i]);
-    orAll |= hits[i];
-    andAll &= hits[i];
-  }
-  if (n < 4096) {
-    std::sort(hits, hits + n);
-  } else {
-    constexpr int BITS = 11, BUCKETS = 1 << BITS;
-    std::vector<uint64_t> tmp(n);
-    uint64_t* src = hits;
-    uint64_t* dst = tmp.data();
-    const uint64_t varying = orAll ^ andAll;  // bits that differ between some two keys
-    for (int shift = 0; shift < 64; shift += BITS) {
-      if (((varying >> shift) & (BUCKETS - 1)) == 0) continue;
-      uint64_t count[BUCKETS] = {0};
-      for (uint64_t i = 0; i < n; i++) count[(src[i] >> shift) & (BUCKETS - 1)]++;
-      uint64_t sum = 0;
-      for (int b = 0; b < BUCKETS; b++) { uint64_t c = count[b]; count[b] = sum; sum += c; }
-      for (uint64_t i = 0; i < n; i++) dst[count[(src[i] >> shift) & (BUCKETS - 1)]++] = src[i];
-      std::swap(src, dst);
-    }
-    if (src != hits) std::memcpy(hits, src, n * sizeof(uint64_t));
-  }
-  for (uint64_t i = 0; i < n; i++) hits[i] = toHit(hits[i]);
-}
-
 }  // namespace
 
 void havac_free_sequence(DeviceCtx& d) {
@@ -331,6 +294,7 @@ int havac_cuda_invoke_async(havac_cuda_client* c) {
   c->launches = 0;
   for (DeviceCtx& d : c->devs) {
     CK(cudaSetDevice(d.dev));
+    d.hitsSorted = false;
     CK(cudaMemsetAsync(d.dHitCount, 0, sizeof(unsigned long long), d.stream));
     CK(cudaMemsetAsync(d.dTileCounter, 0, sizeof(unsigned int), d.stream));
     CK(cudaMemsetAsync(d.dStatus, 0, sizeof(int), d.stream));
@@ -456,15 +420,18 @@ int havac_cuda_read_hits(havac_cuda_client* c, uint64_t* out, uint64_t cap, uint
   if (n) *n = total;
   if (total == 0) return HAVAC_CUDA_OK;
   if (!out || cap < total) return fail(c, HAVAC_CUDA_E_LENGTH, "hit buffer too small: " + std::to_string(total) + " hits");
+  // each device sorts its own hits into the FPGA's emission order (hit_postprocess.cu); devices hold
+  // increasing segment ranges, so laying the lists end to end in device order IS the global order
   uint64_t off = 0;
   for (DeviceCtx& d : c->devs) {
     if (!d.hitCount) continue;
+    rc = havac_sort_hits_on_device(c, d);
+    if (rc) return rc;
     CK(cudaSetDevice(d.dev));
     CK(cudaMemcpy(out + off, d.dHits, d.hitCount * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     c->d2hBytes += d.hitCount * sizeof(uint64_t);
     off += d.hitCount;
   }
-  sort_emission_order(out, total);
   return HAVAC_CUDA_OK;
 }
 

@@ -1,0 +1,287 @@
+// hit_postprocess.cu -- what happens to the raw hit words after the search, on the device
+// (SURVEY.md 8f-2):
+//   * emission order: the FPGA writes hits by (segment, row, cell) ascending (device/HavacHls.cpp:
+//     131-162: outer loop over segments, inner over rows, sieve in cell order). The SSV kernel
+//     finds them by diagonal band, so they are sorted here: the key seg<<38 | row<<14 | cell is a
+//     bit permutation of the hit word; an LSD radix sort (8-bit digits, constant digits skipped)
+//     orders the keys, which are then turned back into hit words.
+//   * resolution: Havac::getHitsFromFinishedRun (host/Havac.cpp:145-187) maps every hit to
+//     (sequenceIndex, positionInSequence) with fastaVectorGetLocalSequencePositionFromGlobal
+//     (FastaVector/src/FastaVector.c:345-373: linear scan, INCLUSIVE end test) and to
+//     (phmmIndex, phmmPosition) with a prefix-sum search (host/Havac.cpp:104-142); here both are
+//     binary searches, one thread per hit, with the same answers.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "client_internal.cuh"
+
+namespace {
+
+constexpr int STHREADS = 256;
+constexpr int ITEMS = 16;
+constexpr int TILE = STHREADS * ITEMS;
+constexpr unsigned FULLMASK = 0xffffffffu;
+
+__host__ __device__ __forceinline__ unsigned long long hit_to_key(unsigned long long h) {
+  return ((h >> 14) & 0x3ffffffull) << 38 | (h >> 40) << 14 | (h & 0x3fffull);
+}
+__host__ __device__ __forceinline__ unsigned long long key_to_hit(unsigned long long k) {
+  return (k & 0x3fffull) | (k >> 38) << 14 | ((k >> 14) & 0xffffffull) << 40;
+}
+
+// hits -> keys in place; OR and AND of all keys tell which digits vary at all
+__global__ void hits_to_keys(unsigned long long* __restrict__ v, unsigned long long n, unsigned long long* __restrict__ orAnd) {
+  unsigned long long o = 0, a = ~0ull;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+    const unsigned long long k = hit_to_key(v[i]);
+    v[i] = k;
+    o |= k;
+    a &= k;
+  }
+#pragma unroll
+  for (int off = 16; off; off >>= 1) {
+    o |= __shfl_xor_sync(FULLMASK, o, off);
+    a &= __shfl_xor_sync(FULLMASK, a, off);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicOr(orAnd, o);
+    atomicAnd(orAnd + 1, a);
+  }
+}
+
+__global__ void keys_to_hits(unsigned long long* __restrict__ v, unsigned long long n) {
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x)
+    v[i] = key_to_hit(v[i]);
+}
+
+// digit histogram of one tile; counts are stored digit-major ([digit][block]) so that one exclusive
+// scan over the whole array yields, for every (digit, block), where that block's keys of that digit go
+__global__ void __launch_bounds__(STHREADS) radix_count(const unsigned long long* __restrict__ keys, unsigned long long n, int shift,
+                                                        unsigned* __restrict__ counts, unsigned nBlocks) {
+  __shared__ unsigned hist[256];
+  hist[threadIdx.x] = 0;
+  __syncthreads();
+  const unsigned long long base = (unsigned long long)blockIdx.x * TILE;
+#pragma unroll 4
+  for (int r = 0; r < ITEMS; r++) {
+    const unsigned long long i = base + (unsigned long long)r * STHREADS + threadIdx.x;
+    if (i < n) atomicAdd(&hist[(keys[i] >> shift) & 255u], 1u);
+  }
+  __syncthreads();
+  counts[(size_t)threadIdx.x * nBlocks + blockIdx.x] = hist[threadIdx.x];
+}
+
+// one CTA: exclusive scan of `total` 32-bit counters in place
+__global__ void __launch_bounds__(1024) scan_exclusive(unsigned* __restrict__ v, unsigned long long total) {
+  __shared__ unsigned part[1024];
+  const unsigned long long per = (total + 1023) / 1024;
+  const unsigned long long a = min((unsigned long long)threadIdx.x * per, total), b = min(a + per, total);
+  unsigned s = 0;
+  for (unsigned long long i = a; i < b; i++) s += v[i];
+  part[threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned acc = 0;
+    for (int t = 0; t < 1024; t++) {
+      const unsigned mine = part[t];
+      part[t] = acc;
+      acc += mine;
+    }
+  }
+  __syncthreads();
+  s = part[threadIdx.x];
+  for (unsigned long long i = a; i < b; i++) {
+    const unsigned c = v[i];
+    v[i] = s;
+    s += c;
+  }
+}
+
+// stable scatter of one tile: keys keep their order within a digit (tile order = round, warp, lane)
+__global__ void __launch_bounds__(STHREADS) radix_scatter(const unsigned long long* __restrict__ in, unsigned long long* __restrict__ out,
+                                                          unsigned long long n, int shift, const unsigned* __restrict__ offsets,
+                                                          unsigned nBlocks) {
+  __shared__ unsigned warpCnt[STHREADS / 32][256];
+  __shared__ unsigned running[256];
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  running[threadIdx.x] = offsets[(size_t)threadIdx.x * nBlocks + blockIdx.x];
+  const unsigned long long base = (unsigned long long)blockIdx.x * TILE;
+  for (int r = 0; r < ITEMS; r++) {
+#pragma unroll
+    for (int w = 0; w < STHREADS / 32; w++) warpCnt[w][threadIdx.x] = 0;
+    __syncthreads();
+    const unsigned long long i = base + (unsigned long long)r * STHREADS + threadIdx.x;
+    const bool valid = i < n;
+    const unsigned long long key = valid ? in[i] : 0ull;
+    const unsigned digit = valid ? (unsigned)((key >> shift) & 255u) : 256u;
+    const unsigned same = __match_any_sync(FULLMASK, digit);
+    const unsigned rank = __popc(same & ((1u << lane) - 1u));
+    if (valid && rank == 0) warpCnt[warp][digit] = __popc(same);
+    __syncthreads();
+    if (valid) {
+      unsigned at = running[digit] + rank;
+      for (unsigned w = 0; w < warp; w++) at += warpCnt[w][digit];
+      out[at] = key;
+    }
+    __syncthreads();
+    unsigned add = 0;
+#pragma unroll
+    for (int w = 0; w < STHREADS / 32; w++) add += warpCnt[w][threadIdx.x];
+    running[threadIdx.x] += add;
+    __syncthreads();
+  }
+}
+
+// one thread per (sorted) hit; sequenceIndex = 0xffffffff marks a hit in the zero padding, which the
+// reference drops (host/Havac.cpp:169-173)
+__global__ void resolve_hits(const unsigned long long* __restrict__ hits, unsigned long long n,
+                             const unsigned long long* __restrict__ seqEnd, unsigned nSeq, const unsigned* __restrict__ prefix,
+                             unsigned nModels, unsigned long long* __restrict__ seqPos, unsigned* __restrict__ seqIdx,
+                             unsigned* __restrict__ phmmPos, unsigned* __restrict__ phmmIdx) {
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+    const unsigned long long h = hits[i];
+    const unsigned long long pos = ((h >> 14) & 0x3ffffffull) * (unsigned long long)SEG + (h & 0x3fffull);
+    const unsigned row = (unsigned)(h >> 40);
+    // first record whose end offset is >= pos (the reference's `<=` test, FastaVector.c:361)
+    unsigned lo = 0, hi = nSeq;
+    while (lo < hi) {
+      const unsigned mid = lo + (hi - lo) / 2;
+      if (seqEnd[mid] >= pos) hi = mid;
+      else lo = mid + 1;
+    }
+    // last model whose first row is <= row (prefix[0] = 0, so there always is one)
+    unsigned a = 0, b = nModels;
+    while (b - a > 1) {
+      const unsigned mid = a + (b - a) / 2;
+      if (prefix[mid] <= row) a = mid;
+      else b = mid;
+    }
+    seqIdx[i] = lo == nSeq ? 0xffffffffu : lo;
+    seqPos[i] = pos - (lo == 0 || lo == nSeq ? 0ull : seqEnd[lo - 1]);
+    phmmIdx[i] = a;
+    phmmPos[i] = row - prefix[a];
+  }
+}
+
+struct Frees {
+  std::vector<void*> p;
+  ~Frees() { for (void* q : p) cudaFree(q); }
+};
+
+}  // namespace
+
+// Sorts the hitCount raw hits of device d into emission order, in place in d.dHits.
+int havac_sort_hits_on_device(havac_cuda_client* c, DeviceCtx& d) {
+  const unsigned long long n = d.hitCount;
+  if (d.hitsSorted || n < 2) { d.hitsSorted = true; return HAVAC_CUDA_OK; }
+  if (n >= (1ull << 32)) return havac_fail(c, HAVAC_CUDA_E_LENGTH, "more than 2^32 hits on one device");
+  CK(cudaSetDevice(d.dev));
+  cudaStream_t st = d.stream;
+  Frees frees;
+  auto dalloc = [&](void** p, size_t bytes) {
+    cudaError_t e = cudaMalloc(p, bytes);
+    if (e == cudaSuccess) frees.p.push_back(*p);
+    return e;
+  };
+  const unsigned nBlocks = (unsigned)((n + TILE - 1) / TILE);
+  unsigned long long *dTmp = nullptr, *dOrAnd = nullptr;
+  unsigned* dCounts = nullptr;
+  CK(dalloc((void**)&dTmp, n * 8));
+  CK(dalloc((void**)&dCounts, (size_t)256 * nBlocks * sizeof(unsigned)));
+  CK(dalloc((void**)&dOrAnd, 16));
+  const unsigned long long init[2] = {0ull, ~0ull};
+  CK(cudaMemcpyAsync(dOrAnd, init, sizeof init, cudaMemcpyHostToDevice, st));
+  const unsigned grid = (unsigned)std::min<unsigned long long>((n + 255) / 256, 148ull * 16);
+  hits_to_keys<<<grid, 256, 0, st>>>(d.dHits, n, dOrAnd);
+  unsigned long long orAnd[2];
+  CK(cudaMemcpyAsync(orAnd, dOrAnd, sizeof orAnd, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  const unsigned long long varying = orAnd[0] ^ orAnd[1];
+  unsigned long long* src = d.dHits;
+  unsigned long long* dst = dTmp;
+  for (int shift = 0; shift < 64; shift += 8) {
+    if (((varying >> shift) & 255ull) == 0) continue;
+    radix_count<<<nBlocks, STHREADS, 0, st>>>(src, n, shift, dCounts, nBlocks);
+    scan_exclusive<<<1, 1024, 0, st>>>(dCounts, (unsigned long long)256 * nBlocks);
+    radix_scatter<<<nBlocks, STHREADS, 0, st>>>(src, dst, n, shift, dCounts, nBlocks);
+    std::swap(src, dst);
+  }
+  keys_to_hits<<<grid, 256, 0, st>>>(src, n);
+  if (src != d.dHits) CK(cudaMemcpyAsync(d.dHits, src, n * 8, cudaMemcpyDeviceToDevice, st));
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(st));
+  d.hitsSorted = true;
+  return HAVAC_CUDA_OK;
+}
+
+extern "C" int havac_cuda_resolve_hits(havac_cuda_client* c, const uint64_t* sequenceEnd, uint64_t nSequences,
+                                       const uint32_t* modelLength, uint32_t nModels, uint64_t* sequencePosition,
+                                       uint32_t* sequenceIndex, uint32_t* phmmPosition, uint32_t* phmmIndex, uint64_t cap,
+                                       uint64_t* nOut) {
+  if (!c || !nOut || (!sequenceEnd && nSequences) || !modelLength || nModels == 0) return HAVAC_CUDA_E_INVALID;
+  uint64_t total = 0;
+  int rc = havac_cuda_num_hits(c, &total);  // E_LOGIC before a run, E_OVERFLOW after an overflowed one
+  if (rc) return rc;
+  *nOut = total;  // upper bound until the padding hits are dropped below
+  if (cap == 0 || total == 0) return HAVAC_CUDA_OK;
+  if (cap < total || !sequencePosition || !sequenceIndex || !phmmPosition || !phmmIndex)
+    return havac_fail(c, HAVAC_CUDA_E_LENGTH, "hit arrays too small: " + std::to_string(total) + " hits");
+  if (nSequences >= (1ull << 32)) return havac_fail(c, HAVAC_CUDA_E_LENGTH, "more than 2^32 records");
+  std::vector<unsigned> prefix(nModels);
+  for (uint32_t i = 0, acc = 0; i < nModels; i++) {  // generatePhmmLenPrefixSums, host/Havac.cpp:104-116
+    prefix[i] = acc;
+    acc += modelLength[i];
+  }
+  uint64_t kept = 0;
+  for (DeviceCtx& d : c->devs) {  // devices hold increasing segment ranges: device order is emission order
+    const unsigned long long n = d.hitCount;
+    if (!n) continue;
+    rc = havac_sort_hits_on_device(c, d);
+    if (rc) return rc;
+    CK(cudaSetDevice(d.dev));
+    Frees frees;
+    auto dalloc = [&](void** p, size_t bytes) {
+      cudaError_t e = cudaMalloc(p, bytes ? bytes : 16);
+      if (e == cudaSuccess) frees.p.push_back(*p);
+      return e;
+    };
+    unsigned long long *dEnd = nullptr, *dPos = nullptr;
+    unsigned *dPrefix = nullptr, *dSeqIdx = nullptr, *dPhmmPos = nullptr, *dPhmmIdx = nullptr;
+    CK(dalloc((void**)&dEnd, nSequences * 8));
+    CK(dalloc((void**)&dPrefix, (size_t)nModels * 4));
+    CK(dalloc((void**)&dPos, n * 8));
+    CK(dalloc((void**)&dSeqIdx, n * 4));
+    CK(dalloc((void**)&dPhmmPos, n * 4));
+    CK(dalloc((void**)&dPhmmIdx, n * 4));
+    CK(cudaMemcpyAsync(dEnd, sequenceEnd, nSequences * 8, cudaMemcpyHostToDevice, d.stream));
+    CK(cudaMemcpyAsync(dPrefix, prefix.data(), (size_t)nModels * 4, cudaMemcpyHostToDevice, d.stream));
+    const unsigned grid = (unsigned)std::min<unsigned long long>((n + 255) / 256, 148ull * 16);
+    resolve_hits<<<grid, 256, 0, d.stream>>>(d.dHits, n, dEnd, (unsigned)nSequences, dPrefix, nModels, dPos, dSeqIdx, dPhmmPos, dPhmmIdx);
+    CK(cudaGetLastError());
+    // straight into the caller's arrays at the running offset, then squeeze out the padding hits
+    CK(cudaMemcpyAsync(sequencePosition + kept, dPos, n * 8, cudaMemcpyDeviceToHost, d.stream));
+    CK(cudaMemcpyAsync(sequenceIndex + kept, dSeqIdx, n * 4, cudaMemcpyDeviceToHost, d.stream));
+    CK(cudaMemcpyAsync(phmmPosition + kept, dPhmmPos, n * 4, cudaMemcpyDeviceToHost, d.stream));
+    CK(cudaMemcpyAsync(phmmIndex + kept, dPhmmIdx, n * 4, cudaMemcpyDeviceToHost, d.stream));
+    CK(cudaStreamSynchronize(d.stream));
+    c->h2dBytes += nSequences * 8 + (uint64_t)nModels * 4;
+    c->d2hBytes += n * 20;
+    uint64_t w = kept;
+    for (uint64_t r = kept; r < kept + n; r++) {
+      if (sequenceIndex[r] == 0xffffffffu) continue;
+      if (w != r) {
+        sequencePosition[w] = sequencePosition[r];
+        sequenceIndex[w] = sequenceIndex[r];
+        phmmPosition[w] = phmmPosition[r];
+        phmmIndex[w] = phmmIndex[r];
+      }
+      w++;
+    }
+    kept = w;
+  }
+  *nOut = kept;
+  return HAVAC_CUDA_OK;
+}

@@ -374,7 +374,7 @@ struct RowGroups<BLOCK_ROWS / 4> {
                                              const uint2*, const uint4*) {}
 };
 
-__global__ void __launch_bounds__(THREADS, 2) ssv_f16x2_kernel(const SsvParams prm) {
+__global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_kernel(const SsvParams prm) {
   extern __shared__ __align__(16) unsigned char smemRaw[];
   FastSmem& sm = *reinterpret_cast<FastSmem*>(smemRaw);
   const int tid = threadIdx.x;

@@ -36,7 +36,10 @@ enum : int { SSV_STATUS_OVERFLOW = 1, SSV_STATUS_ABORTED = 2 };
 
 // Kernel geometry of the fast path (see ssv_kernels.cu).
 constexpr int SSV_R = 16;            // fp16x2 state registers per thread (2 diagonals each)
-constexpr int SSV_THREADS = 256;
+#ifndef SSV_THREADS_V
+#define SSV_THREADS_V 256
+#endif
+constexpr int SSV_THREADS = SSV_THREADS_V;
 constexpr int SSV_TILE_DIAGS = SSV_THREADS * 2 * SSV_R;  // 8192
 #ifndef SSV_ROW_CHUNK_V
 #define SSV_ROW_CHUNK_V 2048  // 512 -> 2048 measured +1.9 % (fewer CTA-wide barriers per tile)

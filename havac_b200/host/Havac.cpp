@@ -141,8 +141,24 @@ vector<HavacHit> havacResolveHits(const vector<uint64_t>& rawHits, const FastaSe
 }
 
 vector<HavacHit> Havac::getHitsFromFinishedRun() {
-  vector<uint64_t> rawHits = this->hwClient->getHitList();
-  return havacResolveHits(rawHits, this->fasta, this->models.lengthPrefixSums());
+  // sorted into emission order and resolved on the device; havacResolveHits above is
+  // the same mapping on the host (HAVAC_HOST_RESOLVE=1 selects it; tests compare the two)
+  const char* forceHost = std::getenv("HAVAC_HOST_RESOLVE");
+  if (forceHost && forceHost[0] == '1') {
+    vector<uint64_t> rawHits = this->hwClient->getHitList();
+    return havacResolveHits(rawHits, this->fasta, this->models.lengthPrefixSums());
+  }
+  vector<uint32_t> lengths;
+  lengths.reserve(this->models.count());
+  for (const PhmmModel& m : this->models.models()) lengths.push_back(m.modelLength);
+  vector<uint64_t> sequencePosition;
+  vector<uint32_t> sequenceIndex, phmmPosition, phmmIndex;
+  this->hwClient->resolveHits(this->fasta.sequenceEndPositions(), lengths, sequencePosition, sequenceIndex, phmmPosition, phmmIndex);
+  vector<HavacHit> resolved;
+  resolved.reserve(sequencePosition.size());
+  for (size_t i = 0; i < sequencePosition.size(); i++)
+    resolved.push_back(HavacHit(sequencePosition[i], sequenceIndex[i], phmmPosition[i], phmmIndex[i]));
+  return resolved;
 }
 
 HavacHit::HavacHit(const uint64_t sequencePosition, const uint32_t sequenceIndex, const uint32_t phmmPosition,

@@ -99,6 +99,28 @@ std::vector<uint8_t> HavacHwClient::readSequence() {
   return out;
 }
 
+void HavacHwClient::resolveHits(const std::vector<uint64_t>& sequenceEndPositions, const std::vector<uint32_t>& modelLengths,
+                                std::vector<uint64_t>& sequencePosition, std::vector<uint32_t>& sequenceIndex,
+                                std::vector<uint32_t>& phmmPosition, std::vector<uint32_t>& phmmIndex) {
+  uint64_t n = 0;
+  check(havac_cuda_num_hits(handle, &n), "getHitList");
+  std::printf("client reported %llu hits\n", (unsigned long long)n);  // HavacHwClient.cpp:189
+  sequencePosition.resize(n);
+  sequenceIndex.resize(n);
+  phmmPosition.resize(n);
+  phmmIndex.resize(n);
+  uint64_t kept = 0;
+  if (n)
+    check(havac_cuda_resolve_hits(handle, sequenceEndPositions.data(), sequenceEndPositions.size(), modelLengths.data(),
+                                  (uint32_t)modelLengths.size(), sequencePosition.data(), sequenceIndex.data(),
+                                  phmmPosition.data(), phmmIndex.data(), n, &kept),
+          "getHitsFromFinishedRun");
+  sequencePosition.resize(kept);
+  sequenceIndex.resize(kept);
+  phmmPosition.resize(kept);
+  phmmIndex.resize(kept);
+}
+
 void HavacHwClient::setSegmentRange(uint64_t segBegin, uint64_t segEnd) {
   check(havac_cuda_set_segment_range(handle, segBegin, segEnd), "setSegmentRange");
 }

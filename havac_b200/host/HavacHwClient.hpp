@@ -51,6 +51,11 @@ public:
   void ingestFasta(const uint8_t* text, uint64_t nBytes, uint8_t (*resolve)(void*, unsigned char), void* user,
                    std::vector<uint64_t>& sequenceEndPositions, std::vector<uint64_t>& headerByteOffsets);
   std::vector<uint8_t> readSequence();
+  // Hits of the finished run, sorted and resolved on the device (havac_cuda_resolve_hits): four
+  // parallel arrays in emission order, padding hits dropped.
+  void resolveHits(const std::vector<uint64_t>& sequenceEndPositions, const std::vector<uint32_t>& modelLengths,
+                   std::vector<uint64_t>& sequencePosition, std::vector<uint32_t>& sequenceIndex,
+                   std::vector<uint32_t>& phmmPosition, std::vector<uint32_t>& phmmIndex);
 
   // harness helpers (no reference counterpart)
   void setSegmentRange(uint64_t segBegin, uint64_t segEnd);

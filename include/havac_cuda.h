@@ -100,6 +100,17 @@ int havac_cuda_abort(havac_cuda_client* c, int* state);
 int havac_cuda_num_hits(havac_cuda_client* c, uint64_t* n);
 int havac_cuda_read_hits(havac_cuda_client* c, uint64_t* out, uint64_t cap, uint64_t* n);
 
+/* Hits of the finished run resolved ON THE DEVICE to the four numbers of a HavacHit, in emission
+ * order, hits in the zero padding dropped: stands for the loop of Havac::getHitsFromFinishedRun
+ * (host/Havac.cpp:145-187) with fastaVectorGetLocalSequencePositionFromGlobal (FastaVector/src/
+ * FastaVector.c:345-373, inclusive end test kept) and the model prefix-sum search
+ * (host/Havac.cpp:104-142). `sequenceEnd` = FastaVector's sequenceEndPosition per record,
+ * `modelLength` = LENG per model. Call with cap = 0 to learn an upper bound of *n. */
+int havac_cuda_resolve_hits(havac_cuda_client* c, const uint64_t* sequenceEnd, uint64_t nSequences,
+                            const uint32_t* modelLength, uint32_t nModels, uint64_t* sequencePosition,
+                            uint32_t* sequenceIndex, uint32_t* phmmPosition, uint32_t* phmmIndex, uint64_t cap,
+                            uint64_t* n);
+
 /* FASTA text -> device-resident packed sequence, parsed and packed ON THE DEVICE. For a client
  * that holds no sequence yet this stands for fastaVectorReadFasta (FastaVector/src/FastaVector.c:
  * 54-168) + SequencePreprocessor (host/sequence/SequencePreprocessor.cpp:9-85) + writeSequence
