@@ -29,7 +29,7 @@ EXPORTS = [
     "havac_cuda_set_segment_range", "havac_cuda_invoke_async", "havac_cuda_state", "havac_cuda_wait",
     "havac_cuda_abort", "havac_cuda_num_hits", "havac_cuda_read_hits", "havac_cuda_last_error",
     "havac_cuda_device_time_ms", "havac_cuda_device_count", "havac_cuda_run_stats", "havac_cuda_set_kernel", "havac_cuda_transfer_stats", "havac_cuda_sm_cycles",
-    "havac_cuda_ingest_fasta", "havac_cuda_ingest_records", "havac_cuda_read_sequence", "havac_cuda_resolve_hits",
+    "havac_cuda_ingest_fasta", "havac_cuda_ingest_records", "havac_cuda_read_sequence", "havac_cuda_resolve_hits", "havac_cuda_project_phmm", "havac_cuda_read_phmm",
 ]
 
 
@@ -59,6 +59,8 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     L.havac_cuda_destroy.argtypes = [vp]
     L.havac_cuda_write_sequence.argtypes = [vp, vp, u64]
     L.havac_cuda_write_phmm.argtypes = [vp, vp, u64]
+    L.havac_cuda_project_phmm.argtypes = [vp, vp, u64, vp, vp, u32]
+    L.havac_cuda_read_phmm.argtypes = [vp, vp, u64, C.POINTER(u64)]
     L.havac_cuda_set_segment_range.argtypes = [vp, u64, u64]
     L.havac_cuda_invoke_async.argtypes = [vp]
     L.havac_cuda_state.argtypes = [vp, C.POINTER(C.c_int)]
@@ -119,6 +121,22 @@ class HavacHwClient:
     def writePhmm(self, phmmAsFlattenedArray) -> None:
         a = np.ascontiguousarray(phmmAsFlattenedArray, dtype=np.int8).reshape(-1)
         self._ck(self._L.havac_cuda_write_phmm(self._h, a.ctypes.data, a.nbytes))
+
+    def projectPhmm(self, negLogEmissions, modelLengths, scaleFactors) -> None:
+        """Score table built on the device from [rows, 4] float emissions (havac_cuda_project_phmm)."""
+        e = np.ascontiguousarray(negLogEmissions, dtype=np.float32).reshape(-1, 4)
+        lens = np.ascontiguousarray(modelLengths, dtype=np.uint32)
+        scale = np.ascontiguousarray(scaleFactors, dtype=np.float32)
+        if len(lens) != len(scale):
+            raise ValueError("one scale factor per model")
+        self._ck(self._L.havac_cuda_project_phmm(self._h, e.ctypes.data, e.shape[0], lens.ctypes.data, scale.ctypes.data, len(lens)))
+
+    def readPhmm(self) -> np.ndarray:
+        n = C.c_uint64(0)
+        self._ck(self._L.havac_cuda_read_phmm(self._h, None, 0, C.byref(n)))
+        buf = np.zeros(n.value, dtype=np.int8)
+        self._ck(self._L.havac_cuda_read_phmm(self._h, buf.ctypes.data, buf.nbytes, C.byref(n)))
+        return buf.reshape(-1, 4)
 
     def invokeHavacSsvAsync(self) -> None:
         self._ck(self._L.havac_cuda_invoke_async(self._h))

@@ -285,6 +285,71 @@ int havac_cuda_write_phmm(havac_cuda_client* c, const int8_t* flat, uint64_t nBy
   return HAVAC_CUDA_OK;
 }
 
+int havac_cuda_project_phmm(havac_cuda_client* c, const float* negLogEmissions, uint64_t nRows, const uint32_t* modelLength,
+                            const float* scaleFactor, uint32_t nModels) {
+  if (!c || (!negLogEmissions && nRows) || (nModels && (!modelLength || !scaleFactor))) return HAVAC_CUDA_E_INVALID;
+  const uint64_t nBytes = nRows * 4;
+  if (nBytes >= 1024ull * 1024 * 1024)  // host/HavacHwClient.cpp:121-125
+    return fail(c, HAVAC_CUDA_E_LENGTH, "model length must be less than 1GiB. length requested: " + std::to_string(nBytes) + " bytes.");
+  if (nRows > MAX_ROWS) return fail(c, HAVAC_CUDA_E_LENGTH, "more than 2^24 model positions: the hit word holds the row in 24 bits");
+  if (c->launched && !c->finished) return fail(c, HAVAC_CUDA_E_LOGIC, "a run is in flight");
+  std::vector<uint32_t> firstRow(nModels);
+  std::vector<float> alphaBeta(2 * (size_t)nModels);
+  uint64_t at = 0;
+  const float LOG2_E = 1.44269504089;  // PhmmReprojection.cpp:113-115
+  for (uint32_t m = 0; m < nModels; m++) {
+    firstRow[m] = (uint32_t)at;
+    at += modelLength[m];
+    alphaBeta[2 * m] = 2 * scaleFactor[m];
+    alphaBeta[2 * m + 1] = LOG2_E * scaleFactor[m];
+  }
+  if (at != nRows) return fail(c, HAVAC_CUDA_E_LENGTH, "model lengths do not add up to the number of emission rows");
+  c->nRows = (uint32_t)nRows;
+  for (DeviceCtx& d : c->devs) {
+    if (c->nRows == 0) { free_table(d); continue; }
+    CK(cudaSetDevice(d.dev));
+    if (nBytes != d.tabCap) {
+      free_table(d);
+      d.rowsPadded = (c->nRows + SSV_ROW_CHUNK - 1) / SSV_ROW_CHUNK * SSV_ROW_CHUNK;
+      CK(cudaMalloc(&d.dTab8, nBytes));
+      CK(cudaMalloc(&d.dTab16, (size_t)d.rowsPadded * sizeof(uint2)));
+      d.tabCap = nBytes;
+    }
+    float *dEm = nullptr, *dAb = nullptr;
+    uint32_t* dFirst = nullptr;
+    CK(cudaMalloc(&dEm, nRows * 16));
+    cudaError_t e1 = cudaMalloc(&dAb, alphaBeta.size() * 4), e2 = cudaMalloc(&dFirst, firstRow.size() * 4);
+    auto drop = [&] { cudaFree(dEm); cudaFree(dAb); cudaFree(dFirst); };
+    if (e1 != cudaSuccess || e2 != cudaSuccess) { drop(); return fail(c, HAVAC_CUDA_E_NOMEM, "cudaMalloc: out of device memory"); }
+    cudaError_t e = cudaMemcpyAsync(dEm, negLogEmissions, nRows * 16, cudaMemcpyHostToDevice, d.stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dAb, alphaBeta.data(), alphaBeta.size() * 4, cudaMemcpyHostToDevice, d.stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dFirst, firstRow.data(), firstRow.size() * 4, cudaMemcpyHostToDevice, d.stream);
+    if (e == cudaSuccess) {
+      ssv_launch_project_table(dEm, c->nRows, dFirst, dAb, nModels, d.dTab8, d.stream);
+      ssv_launch_table_prep(d.dTab8, c->nRows, d.dTab16, d.rowsPadded, d.stream);
+      e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(d.stream);
+    drop();
+    if (e != cudaSuccess) return fail(c, HAVAC_CUDA_E_RUNTIME, std::string("project_phmm: ") + cudaGetErrorString(e));
+    c->h2dBytes += nRows * 16 + alphaBeta.size() * 4 + firstRow.size() * 4;
+  }
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_read_phmm(havac_cuda_client* c, int8_t* flatScores, uint64_t capBytes, uint64_t* nBytes) {
+  if (!c) return HAVAC_CUDA_E_INVALID;
+  const uint64_t bytes = (uint64_t)c->nRows * 4;
+  if (nBytes) *nBytes = bytes;
+  if (!flatScores || capBytes == 0 || bytes == 0) return HAVAC_CUDA_OK;
+  if (capBytes < bytes) return fail(c, HAVAC_CUDA_E_LENGTH, "buffer smaller than the resident score table");
+  DeviceCtx& d = c->devs[0];
+  CK(cudaSetDevice(d.dev));
+  CK(cudaMemcpy(flatScores, d.dTab8, bytes, cudaMemcpyDeviceToHost));
+  c->d2hBytes += bytes;
+  return HAVAC_CUDA_OK;
+}
+
 int havac_cuda_invoke_async(havac_cuda_client* c) {
   if (!c) return HAVAC_CUDA_E_INVALID;
   // host/HavacHwClient.cpp:142-147

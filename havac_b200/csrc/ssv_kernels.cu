@@ -82,6 +82,40 @@ __global__ void table_prep_kernel(const int8_t* __restrict__ tab8, uint32_t nRow
 }
 
 // ---------------------------------------------------------------------------------------
+// Score-table projection on the device: negative-log match emissions ->
+// int8 scores at threshold 256, bit for bit the loop of p7HmmProjectForThreshold256
+// (PhmmReprojection/PhmmReprojection.cpp:117-144): float alpha - (e * beta) with the product
+// and the difference rounded separately (no FMA contraction), round() half away from zero,
+// saturate to [-128, 127]. One thread per model position; alpha = 2*scale and
+// beta = log2(e)*scale come per model from the host, which owns the scale-factor arithmetic.
+// ---------------------------------------------------------------------------------------
+__global__ void project_table_kernel(const float4* __restrict__ emissions, uint32_t nRows,
+                                     const uint32_t* __restrict__ modelFirstRow, const float2* __restrict__ alphaBeta,
+                                     uint32_t nModels, uint32_t* __restrict__ tab8) {
+  const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= nRows) return;
+  uint32_t a = 0, b = nModels;  // last model whose first row is <= r
+  while (b - a > 1) {
+    const uint32_t mid = a + (b - a) / 2;
+    if (modelFirstRow[mid] <= r) a = mid;
+    else b = mid;
+  }
+  const float2 ab = alphaBeta[a];
+  const float4 e = emissions[r];
+  const float in[4] = {e.x, e.y, e.z, e.w};
+  uint32_t packed = 0;
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    float v = __fsub_rn(ab.x, __fmul_rn(in[i], ab.y));
+    v = roundf(v);
+    if (v < -128.f) v = -128.f;
+    if (v > 127.f) v = 127.f;
+    packed |= ((uint32_t)(int)v & 0xffu) << (8 * i);
+  }
+  tab8[r] = packed;
+}
+
+// ---------------------------------------------------------------------------------------
 // Plain kernel: one thread per diagonal, integer arithmetic, everything from global memory.
 // The correctness-first variant and the cross-check for the fast path in tests.
 // ---------------------------------------------------------------------------------------
@@ -523,6 +557,13 @@ void ssv_launch_table_prep(const int8_t* tab8, uint32_t nRows, uint2* tab16, uin
                            void* stream) {
   table_prep_kernel<<<(rowsPadded + 255) / 256, 256, 0, (cudaStream_t)stream>>>(tab8, nRows, tab16,
                                                                               rowsPadded);
+}
+
+void ssv_launch_project_table(const float* emissions, uint32_t nRows, const uint32_t* modelFirstRow, const float* alphaBeta,
+                              uint32_t nModels, int8_t* tab8, void* stream) {
+  project_table_kernel<<<(nRows + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const float4*>(emissions), nRows, modelFirstRow, reinterpret_cast<const float2*>(alphaBeta), nModels,
+      reinterpret_cast<uint32_t*>(tab8));
 }
 
 static bool f16x2_prepare() {

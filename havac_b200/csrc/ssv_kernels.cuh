@@ -54,6 +54,8 @@ constexpr int SSV_SUPERBLOCK_BLOCKS = SSV_SUPERBLOCK_BLOCKS_V;  // 32-row blocks
 // host-callable launchers (defined in ssv_kernels.cu); all asynchronous on `stream`.
 void ssv_launch_table_prep(const int8_t* tab8, uint32_t nRows, uint2* tab16, uint32_t rowsPadded,
                            void* stream);
+void ssv_launch_project_table(const float* emissions, uint32_t nRows, const uint32_t* modelFirstRow, const float* alphaBeta,
+                              uint32_t nModels, int8_t* tab8, void* stream);
 void ssv_launch_f16x2(const SsvParams& prm, int numSMs, void* stream);
 void ssv_launch_scalar(const SsvParams& prm, void* stream);
 int ssv_f16x2_ctas_per_sm();

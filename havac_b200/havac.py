@@ -32,7 +32,7 @@ EXPORTS = [
     "havac_host_run_async", "havac_host_wait", "havac_host_abort", "havac_host_state", "havac_host_get_hits",
     "havac_host_device_time_ms", "havac_host_last_error", "havac_host_pack_fasta", "havac_host_project_phmm",
     "havac_host_scale_factor", "havac_host_resolve_hits", "havac_host_srand", "havac_host_sequence_table",
-    "havac_host_read_sequence",
+    "havac_host_read_sequence", "havac_host_read_phmm",
 ]
 
 _lib = None
@@ -58,6 +58,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     L.havac_host_srand.restype = None
     L.havac_host_sequence_table.argtypes = [vp, vp, u64, C.POINTER(u64)]
     L.havac_host_read_sequence.argtypes = [vp, vp, u64, C.POINTER(u64)]
+    L.havac_host_read_phmm.argtypes = [vp, vp, u64, C.POINTER(u64)]
     L.havac_host_state.argtypes = [vp, C.POINTER(C.c_int)]
     L.havac_host_get_hits.argtypes = [vp, vp, vp, vp, vp, u64, C.POINTER(u64)]
     L.havac_host_device_time_ms.argtypes = [vp, C.POINTER(C.c_float)]
@@ -164,6 +165,14 @@ class Havac:
         buf = np.zeros(n.value, dtype=np.uint8)
         self._ck(self._L.havac_host_read_sequence(self._h, buf.ctypes.data, buf.nbytes, C.byref(n)))
         return buf
+
+    def devicePhmmScores(self) -> np.ndarray:
+        """The int8 score table as the device holds it, [row][A,C,G,T], copied back (harness door)."""
+        n = C.c_uint64(0)
+        self._ck(self._L.havac_host_read_phmm(self._h, None, 0, C.byref(n)))
+        buf = np.zeros(n.value, dtype=np.int8)
+        self._ck(self._L.havac_host_read_phmm(self._h, buf.ctypes.data, buf.nbytes, C.byref(n)))
+        return buf.reshape(-1, 4)
 
     def lastDeviceTimeMs(self) -> float:
         ms = C.c_float(0)

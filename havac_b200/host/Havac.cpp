@@ -22,8 +22,14 @@ Havac::~Havac() {}
 
 void Havac::loadPhmm(const std::string phmmSrc) {
   this->models.readP7Hmm(phmmSrc);  // std::runtime_error on a malformed file (host/Havac.cpp:48-50)
-  this->compressedPhmmScores = this->models.projectForThreshold256(this->requiredPValue);
-  this->hwClient->writePhmm(this->compressedPhmmScores);
+  if (std::getenv("HAVAC_HOST_PROJECT")) {  // the reference's route: project on the host, write the int8 table
+    this->compressedPhmmScores = this->models.projectForThreshold256(this->requiredPValue);
+    this->hwClient->writePhmm(this->compressedPhmmScores);
+  } else {  // scale factors here, the per-position arithmetic and the table layout on the device
+    this->compressedPhmmScores.reset();
+    this->hwClient->projectPhmm(this->models.concatenatedMatchEmissions(), this->models.lengths(),
+                                this->models.threshold256ScaleFactors(this->requiredPValue));
+  }
   this->phmmLoadedToDevice = true;
 }
 

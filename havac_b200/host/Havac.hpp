@@ -61,6 +61,7 @@ public:
   // additions for harnesses (no reference counterpart)
   float lastDeviceTimeMs();
   std::vector<uint8_t> devicePackedSequence() { return hwClient->readSequence(); }  // what the device holds, copied back
+  std::vector<int8_t> devicePhmmScores() { return hwClient->readPhmm(); }  // the int8 score table as the device holds it
   const FastaSequences& sequences() const { return fasta; }
   const PhmmModels& phmms() const { return models; }
 

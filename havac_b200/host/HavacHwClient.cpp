@@ -99,6 +99,22 @@ std::vector<uint8_t> HavacHwClient::readSequence() {
   return out;
 }
 
+void HavacHwClient::projectPhmm(const std::vector<float>& negLogEmissions, const std::vector<uint32_t>& modelLengths,
+                                const std::vector<float>& scaleFactors) {
+  if (modelLengths.size() != scaleFactors.size()) throw std::invalid_argument("projectPhmm: one scale factor per model");
+  check(havac_cuda_project_phmm(handle, negLogEmissions.data(), negLogEmissions.size() / 4, modelLengths.data(),
+                                scaleFactors.data(), (uint32_t)modelLengths.size()),
+        "writePhmm");
+}
+
+std::vector<int8_t> HavacHwClient::readPhmm() {
+  uint64_t n = 0;
+  check(havac_cuda_read_phmm(handle, nullptr, 0, &n), "readPhmm");
+  std::vector<int8_t> out(n);
+  check(havac_cuda_read_phmm(handle, out.data(), out.size(), &n), "readPhmm");
+  return out;
+}
+
 void HavacHwClient::resolveHits(const std::vector<uint64_t>& sequenceEndPositions, const std::vector<uint32_t>& modelLengths,
                                 std::vector<uint64_t>& sequencePosition, std::vector<uint32_t>& sequenceIndex,
                                 std::vector<uint32_t>& phmmPosition, std::vector<uint32_t>& phmmIndex) {

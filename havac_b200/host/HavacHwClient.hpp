@@ -51,6 +51,11 @@ public:
   void ingestFasta(const uint8_t* text, uint64_t nBytes, uint8_t (*resolve)(void*, unsigned char), void* user,
                    std::vector<uint64_t>& sequenceEndPositions, std::vector<uint64_t>& headerByteOffsets);
   std::vector<uint8_t> readSequence();
+  // Negative-log match emissions -> int8 score table on the device (havac_cuda_project_phmm);
+  // stands for p7HmmProjectForThreshold256's loop + PhmmPreprocessor + writePhmm.
+  void projectPhmm(const std::vector<float>& negLogEmissions, const std::vector<uint32_t>& modelLengths,
+                   const std::vector<float>& scaleFactors);
+  std::vector<int8_t> readPhmm();
   // Hits of the finished run, sorted and resolved on the device (havac_cuda_resolve_hits): four
   // parallel arrays in emission order, padding hits dropped.
   void resolveHits(const std::vector<uint64_t>& sequenceEndPositions, const std::vector<uint32_t>& modelLengths,

@@ -39,6 +39,12 @@ public:
   // model position, [A,C,G,T] (PhmmPreprocessor.cpp:9-31). Throws std::runtime_error for a
   // model whose alphabet is not 4 symbols wide or that lacks MAXL / STATS LOCAL MSV.
   std::shared_ptr<std::vector<int8_t>> projectForThreshold256(float pValue) const;
+  // The inputs of the same projection done on the device (havac_cuda_project_phmm): one scale
+  // factor per model (same checks and exceptions as above), the model lengths, and the match
+  // emissions of all models concatenated.
+  std::vector<float> threshold256ScaleFactors(float pValue) const;
+  std::vector<uint32_t> lengths() const;
+  std::vector<float> concatenatedMatchEmissions() const;
 
 private:
   std::vector<PhmmModel> list;

@@ -60,20 +60,43 @@ std::vector<uint32_t> PhmmModels::lengthPrefixSums() const {
   return sums;
 }
 
-std::shared_ptr<std::vector<int8_t>> PhmmModels::projectForThreshold256(float pValue) const {
-  size_t rows = 0;
+std::vector<float> PhmmModels::threshold256ScaleFactors(float pValue) const {
+  std::vector<float> scale;
+  scale.reserve(list.size());
   for (const PhmmModel& m : list) {
     if (m.alphabetCardinality != 4)
       throw std::runtime_error("model '" + m.name + "' is not a nucleotide model: only 4 scores/position are supported.");
     if (m.maxLength == 0 || !m.hasMsvStats)
       throw std::runtime_error("model '" + m.name + "' lacks MAXL or STATS LOCAL MSV, which the threshold projection needs.");
-    rows += m.modelLength;
+    scale.push_back(havacThreshold256ScaleFactor(m.msvGumbelMu, m.msvGumbelLambda, m.maxLength, m.modelLength, pValue));
   }
+  return scale;
+}
+
+std::vector<uint32_t> PhmmModels::lengths() const {
+  std::vector<uint32_t> len;
+  len.reserve(list.size());
+  for (const PhmmModel& m : list) len.push_back(m.modelLength);
+  return len;
+}
+
+std::vector<float> PhmmModels::concatenatedMatchEmissions() const {
+  size_t rows = 0;
+  for (const PhmmModel& m : list) rows += m.modelLength;
+  std::vector<float> all;
+  all.reserve(rows * 4);
+  for (const PhmmModel& m : list) all.insert(all.end(), m.matchEmissionScores.begin(), m.matchEmissionScores.begin() + (size_t)m.modelLength * 4);
+  return all;
+}
+
+std::shared_ptr<std::vector<int8_t>> PhmmModels::projectForThreshold256(float pValue) const {
+  const std::vector<float> scale = threshold256ScaleFactors(pValue);
+  size_t rows = 0;
+  for (const PhmmModel& m : list) rows += m.modelLength;
   auto table = std::make_shared<std::vector<int8_t>>(rows * 4);
-  size_t at = 0;
+  size_t at = 0, i = 0;
   for (const PhmmModel& m : list) {
-    const float scale = havacThreshold256ScaleFactor(m.msvGumbelMu, m.msvGumbelLambda, m.maxLength, m.modelLength, pValue);
-    havacProjectEmissions(m.matchEmissionScores.data(), (size_t)m.modelLength * 4, scale, table->data() + at);
+    havacProjectEmissions(m.matchEmissionScores.data(), (size_t)m.modelLength * 4, scale[i++], table->data() + at);
     at += (size_t)m.modelLength * 4;
   }
   return table;

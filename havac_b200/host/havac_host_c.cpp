@@ -78,6 +78,15 @@ int havac_host_read_sequence(havac_host* h, uint8_t* packed, uint64_t cap, uint6
   });
 }
 
+int havac_host_read_phmm(havac_host* h, int8_t* flatScores, uint64_t cap, uint64_t* n) {
+  if (!h || !n) return -1;
+  return guarded(h, [&] {
+    std::vector<int8_t> buf = h->havac->devicePhmmScores();
+    *n = buf.size();
+    if (flatScores && cap >= buf.size()) std::copy(buf.begin(), buf.end(), flatScores);
+  });
+}
+
 int havac_host_load_phmm(havac_host* h, const char* phmmSrc) {
   if (!h || !phmmSrc) return -1;
   return guarded(h, [&] { h->havac->loadPhmm(phmmSrc); });

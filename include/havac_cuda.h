@@ -100,6 +100,17 @@ int havac_cuda_abort(havac_cuda_client* c, int* state);
 int havac_cuda_num_hits(havac_cuda_client* c, uint64_t* n);
 int havac_cuda_read_hits(havac_cuda_client* c, uint64_t* out, uint64_t cap, uint64_t* n);
 
+/* Score table built ON THE DEVICE from the models' negative-log match emissions ([row][A,C,G,T]
+ * floats as P7HmmReader holds them, models concatenated): stands for the loop of
+ * p7HmmProjectForThreshold256 (PhmmReprojection/PhmmReprojection.cpp:109-145) over all models,
+ * PhmmPreprocessor's concatenation (host/phmm/PhmmPreprocessor.cpp:9-31) and writePhmm, with
+ * byte-identical int8 scores. `scaleFactor[m]` is findThreshold256ScalingFactor of model m
+ * (PhmmReprojection.cpp:36-66), which stays on the host. havac_cuda_read_phmm copies the int8
+ * table back (parity checks). */
+int havac_cuda_project_phmm(havac_cuda_client* c, const float* negLogEmissions, uint64_t nRows, const uint32_t* modelLength,
+                            const float* scaleFactor, uint32_t nModels);
+int havac_cuda_read_phmm(havac_cuda_client* c, int8_t* flatScores, uint64_t capBytes, uint64_t* nBytes);
+
 /* Hits of the finished run resolved ON THE DEVICE to the four numbers of a HavacHit, in emission
  * order, hits in the zero padding dropped: stands for the loop of Havac::getHitsFromFinishedRun
  * (host/Havac.cpp:145-187) with fastaVectorGetLocalSequencePositionFromGlobal (FastaVector/src/

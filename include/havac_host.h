@@ -31,6 +31,8 @@ int havac_host_load_phmm(havac_host* h, const char* phmmSrc);
 void havac_host_srand(unsigned seed);
 int havac_host_sequence_table(havac_host* h, uint64_t* sequenceEnd, uint64_t cap, uint64_t* n);
 int havac_host_read_sequence(havac_host* h, uint8_t* packed, uint64_t cap, uint64_t* n);
+/* The int8 score table as the DEVICE holds it (copied back), to check the device-side projection. */
+int havac_host_read_phmm(havac_host* h, int8_t* flatScores, uint64_t cap, uint64_t* n);
 /* Havac::runHardwareClient / Async / wait / abort / state   host/Havac.cpp:80-102,190-192 */
 int havac_host_run(havac_host* h);
 int havac_host_run_async(havac_host* h);
