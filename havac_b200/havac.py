@@ -32,7 +32,7 @@ EXPORTS = [
     "havac_host_run_async", "havac_host_wait", "havac_host_abort", "havac_host_state", "havac_host_get_hits",
     "havac_host_device_time_ms", "havac_host_last_error", "havac_host_pack_fasta", "havac_host_project_phmm",
     "havac_host_scale_factor", "havac_host_resolve_hits", "havac_host_srand", "havac_host_sequence_table",
-    "havac_host_read_sequence", "havac_host_read_phmm",
+    "havac_host_read_sequence", "havac_host_read_phmm", "havac_host_parse_phmm",
 ]
 
 _lib = None
@@ -66,6 +66,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     L.havac_host_last_error.restype = C.c_char_p
     L.havac_host_pack_fasta.argtypes = [C.c_char_p, C.c_uint, vp, u64, C.POINTER(u64), vp, u64, C.POINTER(u64)]
     L.havac_host_project_phmm.argtypes = [C.c_char_p, C.c_float, vp, u64, C.POINTER(u64), vp, u32, C.POINTER(u32)]
+    L.havac_host_parse_phmm.argtypes = [C.c_char_p, vp, u64, C.POINTER(u64)]
     L.havac_host_scale_factor.argtypes = [C.c_float, C.c_float, u32, u32, C.c_float]
     L.havac_host_scale_factor.restype = C.c_float
     L.havac_host_resolve_hits.argtypes = [vp, u64, vp, u64, vp, u32, vp, vp, vp, vp, C.POINTER(u64)]
@@ -228,6 +229,20 @@ def project_phmm(phmmSrc: str, pValue: float = 0.02) -> Tuple[np.ndarray, np.nda
     if rc:
         _raise(rc, (L.havac_host_last_error(None) or b"").decode())
     return table.reshape(-1, 4), lens
+
+
+def parse_phmm(phmmSrc: str) -> np.ndarray:
+    """.hmm -> match emissions as the reader parsed them, float32 [rows, 4]."""
+    L = load_library()
+    n = C.c_uint64(0)
+    rc = L.havac_host_parse_phmm(os.fspath(phmmSrc).encode(), None, 0, C.byref(n))
+    if rc:
+        _raise(rc, (L.havac_host_last_error(None) or b"").decode())
+    e = np.zeros(n.value, dtype=np.float32)
+    rc = L.havac_host_parse_phmm(os.fspath(phmmSrc).encode(), e.ctypes.data, len(e), C.byref(n))
+    if rc:
+        _raise(rc, (L.havac_host_last_error(None) or b"").decode())
+    return e.reshape(-1, 4)
 
 
 def scale_factor(mu: float, lam: float, maxLength: int, modelLength: int, pValue: float) -> float:

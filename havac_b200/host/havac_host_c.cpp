@@ -181,6 +181,17 @@ int havac_host_project_phmm(const char* phmmSrc, float pValue, int8_t* table, ui
   });
 }
 
+int havac_host_parse_phmm(const char* phmmSrc, float* matchEmissions, uint64_t cap, uint64_t* nFloats) {
+  if (!phmmSrc || !nFloats) return -1;
+  return guarded(nullptr, [&] {
+    PhmmModels m;
+    m.readP7Hmm(phmmSrc);
+    std::vector<float> e = m.concatenatedMatchEmissions();
+    *nFloats = e.size();
+    if (matchEmissions && cap >= e.size()) std::copy(e.begin(), e.end(), matchEmissions);
+  });
+}
+
 float havac_host_scale_factor(float mu, float lambda, uint32_t maxLength, uint32_t modelLength, float pValue) {
   return havacThreshold256ScaleFactor(mu, lambda, maxLength, modelLength, pValue);
 }

@@ -53,6 +53,9 @@ int havac_host_pack_fasta(const char* fastaSrc, unsigned seed, uint8_t* packed, 
 /* .hmm -> flat int8 table at threshold 256 + model lengths (P7HmmReader + PhmmPreprocessor). */
 int havac_host_project_phmm(const char* phmmSrc, float pValue, int8_t* table, uint64_t tableCap, uint64_t* tableBytes,
                             uint32_t* modelLength, uint32_t lengthCap, uint32_t* nModels);
+/* .hmm -> the match emissions as parsed (negative natural logs, models concatenated, 4 per
+ * position), to check the reader's number parsing on its own. */
+int havac_host_parse_phmm(const char* phmmSrc, float* matchEmissions, uint64_t cap, uint64_t* nFloats);
 /* findThreshold256ScalingFactor                             PhmmReprojection.cpp:36-66 */
 float havac_host_scale_factor(float mu, float lambda, uint32_t maxLength, uint32_t modelLength, float pValue);
 /* raw u64 hits -> (sequencePosition, sequenceIndex, phmmPosition, phmmIndex); padding hits dropped. */
