@@ -3,7 +3,9 @@
 // run, hit read-back, total). It compiles unchanged against the reference's host/Havac.hpp; here
 // it links libhavac_host + libhavac_cuda (B200). One JSON line on stdout.
 //
-//   havac_benchmark <device spec | xclbin path> <fasta> <hmm> [p-value]
+//   havac_benchmark <device spec | xclbin path> <fasta> <hmm> [p-value] [both]
+// "both" also searches the reverse complement (Havac::useReverseComplement, this repo's addition;
+// leave it out to compile against the reference's header) and adds crick_* fields.
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -38,6 +40,21 @@ int main(int argc, char** argv) {
     const auto t4 = now();
     std::vector<HavacHit> hits = havac->getHitsFromFinishedRun();
     const auto t5 = now();
+    const bool both = argc > 5 && std::string(argv[5]) == "both";
+    size_t crickHits = 0;
+    double crickReverse = 0, crickRun = 0, crickGet = 0;
+    if (both) {
+      const auto c0 = now();
+      havac->useReverseComplement(true);  // reversed on the device, nothing re-read or re-sent
+      const auto c1 = now();
+      havac->runHardwareClient();
+      const auto c2 = now();
+      crickHits = havac->getHitsFromFinishedRun().size();
+      const auto c3 = now();
+      crickReverse = seconds(c0, c1);
+      crickRun = seconds(c1, c2);
+      crickGet = seconds(c2, c3);
+    }
 
     const double symbols = (double)havac->sequences().symbolCount();
     uint64_t rows = 0;
@@ -47,11 +64,15 @@ int main(int argc, char** argv) {
         "{\"fasta\": \"%s\", \"hmm\": \"%s\", \"p_value\": %g, \"symbols\": %.0f, \"records\": %llu, \"models\": %zu, "
         "\"rows\": %llu, \"hits\": %zu, \"build_s\": %.4f, \"load_phmm_s\": %.4f, \"load_sequence_s\": %.4f, "
         "\"run_s\": %.4f, \"get_hits_s\": %.4f, \"total_s\": %.4f, \"device_ms\": %.3f, \"gcups_device\": %.1f, "
-        "\"gcups_whole_program\": %.1f}\n",
+        "\"gcups_whole_program\": %.1f",
         fastaSrc.c_str(), phmmSrc.c_str(), pValue, symbols, (unsigned long long)havac->sequences().numSequences(),
         (size_t)havac->phmms().count(), (unsigned long long)rows, hits.size(), seconds(t0, t1), seconds(t1, t2),
         seconds(t2, t3), seconds(t3, t4), seconds(t4, t5), seconds(t0, t5), deviceMs,
         symbols * (double)rows / (deviceMs * 1e-3) / 1e9, symbols * (double)rows / seconds(t0, t5) / 1e9);
+    if (both)
+      std::printf(", \"crick_hits\": %zu, \"crick_reverse_s\": %.4f, \"crick_run_s\": %.4f, \"crick_get_hits_s\": %.4f", crickHits,
+                  crickReverse, crickRun, crickGet);
+    std::printf("}\n");
     if (!hits.empty()) std::fprintf(stderr, "first hit: %s\n", hits.front().toString().c_str());
   } catch (const std::exception& e) {
     std::fprintf(stderr, "havac_benchmark: %s\n", e.what());

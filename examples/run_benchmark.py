@@ -39,8 +39,9 @@ def models_with_total(seed, total, lo=60, hi=400):
     return synth.random_models(seed, lens)
 
 
-def run(exe, fasta, hmm, extra):
-    out = subprocess.run([exe, "", fasta, hmm, "0.02"], check=True, capture_output=True, text=True).stdout
+def run(exe, fasta, hmm, extra, both=False):
+    out = subprocess.run([exe, "", fasta, hmm, "0.02"] + (["both"] if both else []), check=True, capture_output=True,
+                         text=True).stdout
     line = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
     line.update(extra)
     for k in ("fasta", "hmm"):
@@ -65,6 +66,7 @@ def main():
         synth.write_fasta(fa, [sym])
         synth.write_hmm(hmm, models)
         run(exe, fa, hmm, {"case": "configs[1] from files: 100 Mbp x 100 models"})
+        run(exe, fa, hmm, {"case": "configs[1] from files, both strands (reverse complement made on the device)"}, both=True)
         # (b) the published series' shape
         sym = synth.random_symbols(22, 50_800_000)
         fa = os.path.join(tmp, "chr22_like.fa")

@@ -30,6 +30,7 @@ EXPORTS = [
     "havac_cuda_abort", "havac_cuda_num_hits", "havac_cuda_read_hits", "havac_cuda_last_error",
     "havac_cuda_device_time_ms", "havac_cuda_device_count", "havac_cuda_run_stats", "havac_cuda_set_kernel", "havac_cuda_transfer_stats", "havac_cuda_sm_cycles",
     "havac_cuda_ingest_fasta", "havac_cuda_ingest_records", "havac_cuda_read_sequence", "havac_cuda_resolve_hits", "havac_cuda_project_phmm", "havac_cuda_read_phmm",
+    "havac_cuda_reverse_complement", "havac_cuda_strand_state",
 ]
 
 
@@ -61,6 +62,9 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     L.havac_cuda_write_phmm.argtypes = [vp, vp, u64]
     L.havac_cuda_project_phmm.argtypes = [vp, vp, u64, vp, vp, u32]
     L.havac_cuda_read_phmm.argtypes = [vp, vp, u64, C.POINTER(u64)]
+    L.havac_cuda_read_sequence.argtypes = [vp, vp, u64, C.POINTER(u64)]
+    L.havac_cuda_reverse_complement.argtypes = [vp, u64]
+    L.havac_cuda_strand_state.argtypes = [vp, C.POINTER(u64)]
     L.havac_cuda_set_segment_range.argtypes = [vp, u64, u64]
     L.havac_cuda_invoke_async.argtypes = [vp]
     L.havac_cuda_state.argtypes = [vp, C.POINTER(C.c_int)]
@@ -137,6 +141,23 @@ class HavacHwClient:
         buf = np.zeros(n.value, dtype=np.int8)
         self._ck(self._L.havac_cuda_read_phmm(self._h, buf.ctypes.data, buf.nbytes, C.byref(n)))
         return buf.reshape(-1, 4)
+
+    def readSequence(self) -> np.ndarray:
+        """The packed sequence as the (single) device holds it, copied back."""
+        n = C.c_uint64(0)
+        self._ck(self._L.havac_cuda_read_sequence(self._h, None, 0, C.byref(n)))
+        buf = np.zeros(n.value, dtype=np.uint8)
+        self._ck(self._L.havac_cuda_read_sequence(self._h, buf.ctypes.data, buf.nbytes, C.byref(n)))
+        return buf
+
+    def reverseComplement(self, nSymbols: int) -> None:
+        """Resident sequence <-> its reverse complement over the first nSymbols symbols, on the device."""
+        self._ck(self._L.havac_cuda_reverse_complement(self._h, nSymbols))
+
+    def mirroredSymbols(self) -> int:
+        n = C.c_uint64(0)
+        self._ck(self._L.havac_cuda_strand_state(self._h, C.byref(n)))
+        return n.value
 
     def invokeHavacSsvAsync(self) -> None:
         self._ck(self._L.havac_cuda_invoke_async(self._h))

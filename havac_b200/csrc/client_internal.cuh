@@ -51,6 +51,7 @@ struct havac_cuda_client {
   unsigned long long hitCap = 16ull << 20;  // per device
   uint64_t segBegin = 0, segEnd = 0;        // 0,0 = whole buffer
   uint64_t seqSegments = 0;                 // segments in the buffer given to write_sequence
+  uint64_t mirrorSymbols = 0;               // N when the resident sequence is the reverse complement over N symbols (strand.cu)
   uint32_t nRows = 0;
   bool launched = false, finished = false, aborted = false;
   int finalState = HAVAC_CUDA_STATE_NEW;

@@ -497,6 +497,7 @@ int havac_cuda_ingest_fasta(havac_cuda_client* c, const uint8_t* text, uint64_t 
     d.colBegin = d.resBegin = 0;
     d.colEnd = d.resEnd = (long long)(segments * SEG);
     c->seqSegments = segments;
+    c->mirrorSymbols = 0;
     return HAVAC_CUDA_OK;
   }
   // sharded clients take the packed buffer through the ordinary path (halo and ranges handled there)

@@ -222,6 +222,7 @@ int havac_cuda_write_sequence(havac_cuda_client* c, const uint8_t* packed, uint6
                                             std::to_string(nBytes) + " bytes.");
   if (c->launched && !c->finished) return fail(c, HAVAC_CUDA_E_LOGIC, "a run is in flight");
   c->seqSegments = nSymbols / SEG;
+  c->mirrorSymbols = 0;
   uint64_t sb = c->segBegin, se = c->segEnd ? c->segEnd : c->seqSegments;
   if (se > c->seqSegments) se = c->seqSegments;
   if (sb > se) sb = se;

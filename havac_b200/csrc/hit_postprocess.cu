@@ -139,12 +139,16 @@ __global__ void __launch_bounds__(STHREADS) radix_scatter(const unsigned long lo
 // reference drops (host/Havac.cpp:169-173)
 __global__ void resolve_hits(const unsigned long long* __restrict__ hits, unsigned long long n,
                              const unsigned long long* __restrict__ seqEnd, unsigned nSeq, const unsigned* __restrict__ prefix,
-                             unsigned nModels, unsigned long long* __restrict__ seqPos, unsigned* __restrict__ seqIdx,
-                             unsigned* __restrict__ phmmPos, unsigned* __restrict__ phmmIdx) {
+                             unsigned nModels, unsigned long long mirrorSymbols, unsigned long long* __restrict__ seqPos,
+                             unsigned* __restrict__ seqIdx, unsigned* __restrict__ phmmPos, unsigned* __restrict__ phmmIdx) {
   for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
     const unsigned long long h = hits[i];
-    const unsigned long long pos = ((h >> 14) & 0x3ffffffull) * (unsigned long long)SEG + (h & 0x3fffull);
+    unsigned long long pos = ((h >> 14) & 0x3ffffffull) * (unsigned long long)SEG + (h & 0x3fffull);
     const unsigned row = (unsigned)(h >> 40);
+    // reverse-complemented sequence (strand.cu): report the forward-strand coordinate of the symbol;
+    // anything at or beyond the mirrored length lies in the padding
+    const bool beyond = mirrorSymbols != 0 && pos >= mirrorSymbols;
+    if (mirrorSymbols != 0 && !beyond) pos = mirrorSymbols - 1 - pos;
     // first record whose end offset is >= pos (the reference's `<=` test, FastaVector.c:361)
     unsigned lo = 0, hi = nSeq;
     while (lo < hi) {
@@ -159,6 +163,7 @@ __global__ void resolve_hits(const unsigned long long* __restrict__ hits, unsign
       if (prefix[mid] <= row) a = mid;
       else b = mid;
     }
+    if (beyond) lo = nSeq;
     seqIdx[i] = lo == nSeq ? 0xffffffffu : lo;
     seqPos[i] = pos - (lo == 0 || lo == nSeq ? 0ull : seqEnd[lo - 1]);
     phmmIdx[i] = a;
@@ -259,7 +264,8 @@ extern "C" int havac_cuda_resolve_hits(havac_cuda_client* c, const uint64_t* seq
     CK(cudaMemcpyAsync(dEnd, sequenceEnd, nSequences * 8, cudaMemcpyHostToDevice, d.stream));
     CK(cudaMemcpyAsync(dPrefix, prefix.data(), (size_t)nModels * 4, cudaMemcpyHostToDevice, d.stream));
     const unsigned grid = (unsigned)std::min<unsigned long long>((n + 255) / 256, 148ull * 16);
-    resolve_hits<<<grid, 256, 0, d.stream>>>(d.dHits, n, dEnd, (unsigned)nSequences, dPrefix, nModels, dPos, dSeqIdx, dPhmmPos, dPhmmIdx);
+    resolve_hits<<<grid, 256, 0, d.stream>>>(d.dHits, n, dEnd, (unsigned)nSequences, dPrefix, nModels, c->mirrorSymbols, dPos, dSeqIdx, dPhmmPos,
+                                              dPhmmIdx);
     CK(cudaGetLastError());
     // straight into the caller's arrays at the running offset, then squeeze out the padding hits
     CK(cudaMemcpyAsync(sequencePosition + kept, dPos, n * 8, cudaMemcpyDeviceToHost, d.stream));

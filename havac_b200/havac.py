@@ -33,6 +33,7 @@ EXPORTS = [
     "havac_host_device_time_ms", "havac_host_last_error", "havac_host_pack_fasta", "havac_host_project_phmm",
     "havac_host_scale_factor", "havac_host_resolve_hits", "havac_host_srand", "havac_host_sequence_table",
     "havac_host_read_sequence", "havac_host_read_phmm", "havac_host_parse_phmm",
+    "havac_host_use_reverse_complement", "havac_host_reverse_complement_packed",
 ]
 
 _lib = None
@@ -59,6 +60,8 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     L.havac_host_sequence_table.argtypes = [vp, vp, u64, C.POINTER(u64)]
     L.havac_host_read_sequence.argtypes = [vp, vp, u64, C.POINTER(u64)]
     L.havac_host_read_phmm.argtypes = [vp, vp, u64, C.POINTER(u64)]
+    L.havac_host_use_reverse_complement.argtypes = [vp, C.c_int]
+    L.havac_host_reverse_complement_packed.argtypes = [vp, u64, u64]
     L.havac_host_state.argtypes = [vp, C.POINTER(C.c_int)]
     L.havac_host_get_hits.argtypes = [vp, vp, vp, vp, vp, u64, C.POINTER(u64)]
     L.havac_host_device_time_ms.argtypes = [vp, C.POINTER(C.c_float)]
@@ -167,6 +170,10 @@ class Havac:
         self._ck(self._L.havac_host_read_sequence(self._h, buf.ctypes.data, buf.nbytes, C.byref(n)))
         return buf
 
+    def useReverseComplement(self, crick: bool) -> None:
+        """True: search the reverse complement of the loaded sequence (hits at forward coordinates)."""
+        self._ck(self._L.havac_host_use_reverse_complement(self._h, 1 if crick else 0))
+
     def devicePhmmScores(self) -> np.ndarray:
         """The int8 score table as the device holds it, [row][A,C,G,T], copied back (harness door)."""
         n = C.c_uint64(0)
@@ -243,6 +250,16 @@ def parse_phmm(phmmSrc: str) -> np.ndarray:
     if rc:
         _raise(rc, (L.havac_host_last_error(None) or b"").decode())
     return e.reshape(-1, 4)
+
+
+def reverse_complement_packed(packed, nSymbols: int) -> np.ndarray:
+    """Reverse complement of a 2-bit packed buffer over its first nSymbols symbols (host form)."""
+    L = load_library()
+    buf = np.array(packed, dtype=np.uint8, copy=True)
+    rc = L.havac_host_reverse_complement_packed(buf.ctypes.data, buf.nbytes, nSymbols)
+    if rc:
+        _raise(rc, (L.havac_host_last_error(None) or b"").decode())
+    return buf
 
 
 def scale_factor(mu: float, lam: float, maxLength: int, modelLength: int, pValue: float) -> float:

@@ -1,5 +1,6 @@
 #include "FastaSequences.hpp"
 
+#include <cstring>
 #include <cstdio>
 #include <cstdlib>
 #include <stdexcept>
@@ -145,4 +146,32 @@ FastaSequences FastaSequences::fromEndPositions(const std::vector<uint64_t>& seq
   f.names.resize(sequenceEndPositions.size());
   f.nSymbols = f.symbolCount();
   return f;
+}
+
+void havacReverseComplementPacked(std::vector<uint8_t>& packed, uint64_t nSymbols) {
+  if (nSymbols > packed.size() * 4) throw std::length_error("reverse complement over more symbols than the buffer holds");
+  // 16 symbols (one little-endian 32-bit word) at a time, out of place: word w takes its symbols
+  // from the two input words around symbol nSymbols-1-16w, as the device kernel does (strand.cu)
+  const uint64_t nWords = (packed.size() + 3) / 4;
+  std::vector<uint32_t> in(nWords + 1, 0u), out(nWords, 0u);
+  std::memcpy(in.data(), packed.data(), packed.size());
+  auto reverseSymbols = [](uint32_t x) -> uint32_t {
+    x = ((x >> 2) & 0x33333333u) | ((x & 0x33333333u) << 2);
+    x = ((x >> 4) & 0x0f0f0f0fu) | ((x & 0x0f0f0f0fu) << 4);
+    return __builtin_bswap32(x);
+  };
+  for (uint64_t w = 0; w < nWords; w++) {
+    const uint64_t first = 16 * w;
+    if (first >= nSymbols) { out[w] = in[w]; continue; }
+    const uint64_t hi = nSymbols - 1 - first, b = hi >> 4;
+    const uint64_t window = ((uint64_t)in[b] << 32) | (b ? in[b - 1] : 0u);
+    uint32_t r = ~reverseSymbols((uint32_t)(window >> (2 * ((unsigned)(hi & 15) + 1))));
+    const uint64_t m = nSymbols - first;
+    if (m < 16) {
+      const uint32_t mask = (1u << (2 * (unsigned)m)) - 1u;
+      r = (r & mask) | (in[w] & ~mask);
+    }
+    out[w] = r;
+  }
+  std::memcpy(packed.data(), out.data(), packed.size());
 }

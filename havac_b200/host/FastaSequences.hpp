@@ -71,4 +71,9 @@ private:
 // operator-precedence slip (`randMod2 << 1 + 1`), whose two low bits are always 0.
 uint8_t havacCompressedSymbol(unsigned char c);
 
+// The packed buffer's reverse complement over its first nSymbols symbols, in place (the padding
+// behind them stays): symbol k becomes 3 - symbol(nSymbols-1-k). The host form of
+// havac_cuda_reverse_complement, for clients that hold a segment range only.
+void havacReverseComplementPacked(std::vector<uint8_t>& packed, uint64_t nSymbols);
+
 #endif

@@ -80,6 +80,7 @@ void Havac::loadSequence(const std::string fastaSrc) {
   // to the records already held, as the reference's FastaVector does; that rare case (the packed
   // buffer is first copied back from the device) and HAVAC_HOST_FASTA=1 take the host reader, which
   // produces the same bytes.
+  if (this->crickStrand) this->useReverseComplement(false);  // an append goes onto the file's strand
   const char* forceHost = std::getenv("HAVAC_HOST_FASTA");
   if (this->fasta.numSequences() == 0 && !(forceHost && forceHost[0] == '1')) {
     MappedFile file(fastaSrc);
@@ -146,12 +147,31 @@ vector<HavacHit> havacResolveHits(const vector<uint64_t>& rawHits, const FastaSe
   return resolved;
 }
 
+void Havac::useReverseComplement(const bool crick) {
+  if (!this->sequenceLoadedToDevice) throw std::logic_error("useReverseComplement: no sequence has been loaded");
+  if (crick == this->crickStrand) return;
+  this->hwClient->reverseComplement(this->fasta.symbolCount());
+  this->crickStrand = crick;
+}
+
 vector<HavacHit> Havac::getHitsFromFinishedRun() {
   // sorted into emission order and resolved on the device; havacResolveHits above is
   // the same mapping on the host (HAVAC_HOST_RESOLVE=1 selects it; tests compare the two)
   const char* forceHost = std::getenv("HAVAC_HOST_RESOLVE");
   if (forceHost && forceHost[0] == '1') {
     vector<uint64_t> rawHits = this->hwClient->getHitList();
+    if (this->crickStrand) {  // reversed coordinates -> forward-strand hit words; padding hits dropped
+      const uint64_t n = this->fasta.symbolCount();
+      vector<uint64_t> forward;
+      forward.reserve(rawHits.size());
+      for (uint64_t h : rawHits) {
+        const uint64_t pos = ((h >> 14) & 0x3ffffffull) * HAVAC_SEGMENT_SYMBOLS + (h & 0x3fffull);
+        if (pos >= n) continue;
+        const uint64_t f = n - 1 - pos;
+        forward.push_back((h & ~0xffffffffffull) | ((f / HAVAC_SEGMENT_SYMBOLS) << 14) | (f % HAVAC_SEGMENT_SYMBOLS));
+      }
+      rawHits.swap(forward);
+    }
     return havacResolveHits(rawHits, this->fasta, this->models.lengthPrefixSums());
   }
   vector<uint32_t> lengths;

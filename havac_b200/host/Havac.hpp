@@ -58,6 +58,15 @@ public:
   vector<HavacHit> getHitsFromFinishedRun();
   enum havac_cmd_state currentHardwareState();
 
+  // The other strand (no reference counterpart: the reference searches the strand in the file and
+  // leaves the reverse complement to a second run on a reversed file). true: the sequence resident
+  // on the device is replaced, there, by its reverse complement; the next run searches the Crick
+  // strand and getHitsFromFinishedRun reports each hit at the FORWARD-strand coordinate of the
+  // symbol that crossed the threshold (record index and position as usual, model positions as
+  // usual). false: back to the strand in the file. loadSequence starts on the file's strand.
+  void useReverseComplement(const bool crick);
+  bool usingReverseComplement() const { return crickStrand; }
+
   // additions for harnesses (no reference counterpart)
   float lastDeviceTimeMs();
   std::vector<uint8_t> devicePackedSequence() { return hwClient->readSequence(); }  // what the device holds, copied back
@@ -74,6 +83,7 @@ private:
   float requiredPValue;
   bool phmmLoadedToDevice = false;
   bool sequenceLoadedToDevice = false;
+  bool crickStrand = false;
   std::string havacXclbinFileSrc;
   const std::string havacKernelName = "HavacKernel";
 };

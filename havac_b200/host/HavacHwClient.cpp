@@ -115,6 +115,10 @@ std::vector<int8_t> HavacHwClient::readPhmm() {
   return out;
 }
 
+void HavacHwClient::reverseComplement(uint64_t nSymbols) {
+  check(havac_cuda_reverse_complement(handle, nSymbols), "reverseComplement");
+}
+
 void HavacHwClient::resolveHits(const std::vector<uint64_t>& sequenceEndPositions, const std::vector<uint32_t>& modelLengths,
                                 std::vector<uint64_t>& sequencePosition, std::vector<uint32_t>& sequenceIndex,
                                 std::vector<uint32_t>& phmmPosition, std::vector<uint32_t>& phmmIndex) {

@@ -56,6 +56,8 @@ public:
   void projectPhmm(const std::vector<float>& negLogEmissions, const std::vector<uint32_t>& modelLengths,
                    const std::vector<float>& scaleFactors);
   std::vector<int8_t> readPhmm();
+  // resident sequence <-> its reverse complement over the first nSymbols symbols (havac_cuda_reverse_complement)
+  void reverseComplement(uint64_t nSymbols);
   // Hits of the finished run, sorted and resolved on the device (havac_cuda_resolve_hits): four
   // parallel arrays in emission order, padding hits dropped.
   void resolveHits(const std::vector<uint64_t>& sequenceEndPositions, const std::vector<uint32_t>& modelLengths,

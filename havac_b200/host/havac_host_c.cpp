@@ -87,6 +87,20 @@ int havac_host_read_phmm(havac_host* h, int8_t* flatScores, uint64_t cap, uint64
   });
 }
 
+int havac_host_use_reverse_complement(havac_host* h, int crick) {
+  if (!h) return -1;
+  return guarded(h, [&] { h->havac->useReverseComplement(crick != 0); });
+}
+
+int havac_host_reverse_complement_packed(uint8_t* packed, uint64_t nBytes, uint64_t nSymbols) {
+  if (!packed && nBytes) return -1;
+  return guarded(nullptr, [&] {
+    std::vector<uint8_t> buf(packed, packed + nBytes);
+    havacReverseComplementPacked(buf, nSymbols);
+    std::copy(buf.begin(), buf.end(), packed);
+  });
+}
+
 int havac_host_load_phmm(havac_host* h, const char* phmmSrc) {
   if (!h || !phmmSrc) return -1;
   return guarded(h, [&] { h->havac->loadPhmm(phmmSrc); });

@@ -111,6 +111,19 @@ int havac_cuda_project_phmm(havac_cuda_client* c, const float* negLogEmissions, 
                             const float* scaleFactor, uint32_t nModels);
 int havac_cuda_read_phmm(havac_cuda_client* c, int8_t* flatScores, uint64_t capBytes, uint64_t* nBytes);
 
+/* The other strand. Replaces the resident sequence, on the device, by its reverse complement over
+ * the first `nSymbols` symbols (the real ones: records and their terminators; the zero padding up
+ * to whole segments stays at the end), so that the next invoke searches the Crick strand, which the
+ * reference leaves to a second run on a reversed file (benchmark/readme.txt:62-64 pins nhmmer to
+ * --watson for the comparison). A second call with the same count restores the forward sequence;
+ * writing or ingesting a sequence resets the state. While reversed, raw hits (read_hits) are in
+ * reversed coordinates and havac_cuda_resolve_hits reports forward-strand positions
+ * (nSymbols - 1 - position; hits in the padding are dropped). Clients limited to a segment range
+ * (set_segment_range) answer E_LOGIC: reverse the packed buffer on the host and write it.
+ * havac_cuda_strand_state: 0 = forward, else the count the sequence is reversed over. */
+int havac_cuda_reverse_complement(havac_cuda_client* c, uint64_t nSymbols);
+int havac_cuda_strand_state(havac_cuda_client* c, uint64_t* mirroredSymbols);
+
 /* Hits of the finished run resolved ON THE DEVICE to the four numbers of a HavacHit, in emission
  * order, hits in the zero padding dropped: stands for the loop of Havac::getHitsFromFinishedRun
  * (host/Havac.cpp:145-187) with fastaVectorGetLocalSequencePositionFromGlobal (FastaVector/src/

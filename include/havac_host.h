@@ -33,6 +33,12 @@ int havac_host_sequence_table(havac_host* h, uint64_t* sequenceEnd, uint64_t cap
 int havac_host_read_sequence(havac_host* h, uint8_t* packed, uint64_t cap, uint64_t* n);
 /* The int8 score table as the DEVICE holds it (copied back), to check the device-side projection. */
 int havac_host_read_phmm(havac_host* h, int8_t* flatScores, uint64_t cap, uint64_t* n);
+/* Havac::useReverseComplement (no reference counterpart): 1 = the next runs search the reverse
+ * complement of the loaded sequence (reversed on the device), hits reported at forward-strand
+ * coordinates; 0 = back to the strand in the file. And the same reversal of a packed buffer on the
+ * host, in place, for clients that hold a segment range only. */
+int havac_host_use_reverse_complement(havac_host* h, int crick);
+int havac_host_reverse_complement_packed(uint8_t* packed, uint64_t nBytes, uint64_t nSymbols);
 /* Havac::runHardwareClient / Async / wait / abort / state   host/Havac.cpp:80-102,190-192 */
 int havac_host_run(havac_host* h);
 int havac_host_run_async(havac_host* h);
