@@ -33,7 +33,7 @@ EXPORTS = [
     "havac_host_device_time_ms", "havac_host_last_error", "havac_host_pack_fasta", "havac_host_project_phmm",
     "havac_host_scale_factor", "havac_host_resolve_hits", "havac_host_srand", "havac_host_sequence_table",
     "havac_host_read_sequence", "havac_host_read_phmm", "havac_host_parse_phmm",
-    "havac_host_use_reverse_complement", "havac_host_reverse_complement_packed",
+    "havac_host_model_names", "havac_host_use_reverse_complement", "havac_host_reverse_complement_packed",
 ]
 
 _lib = None
@@ -60,6 +60,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     L.havac_host_sequence_table.argtypes = [vp, vp, u64, C.POINTER(u64)]
     L.havac_host_read_sequence.argtypes = [vp, vp, u64, C.POINTER(u64)]
     L.havac_host_read_phmm.argtypes = [vp, vp, u64, C.POINTER(u64)]
+    L.havac_host_model_names.argtypes = [C.c_char_p, vp, u64, C.POINTER(u64)]
     L.havac_host_use_reverse_complement.argtypes = [vp, C.c_int]
     L.havac_host_reverse_complement_packed.argtypes = [vp, u64, u64]
     L.havac_host_state.argtypes = [vp, C.POINTER(C.c_int)]
@@ -260,6 +261,21 @@ def reverse_complement_packed(packed, nSymbols: int) -> np.ndarray:
     if rc:
         _raise(rc, (L.havac_host_last_error(None) or b"").decode())
     return buf
+
+
+def model_names(phmmSrc: str) -> List[Tuple[str, str]]:
+    """.hmm -> [(NAME, ACC)] in file order; ACC is "" where the model has none."""
+    L = load_library()
+    n = C.c_uint64(0)
+    rc = L.havac_host_model_names(os.fspath(phmmSrc).encode(), None, 0, C.byref(n))
+    if rc:
+        _raise(rc, (L.havac_host_last_error(None) or b"").decode())
+    buf = C.create_string_buffer(max(1, n.value))
+    rc = L.havac_host_model_names(os.fspath(phmmSrc).encode(), buf, n.value, C.byref(n))
+    if rc:
+        _raise(rc, (L.havac_host_last_error(None) or b"").decode())
+    lines = buf.raw[:n.value].decode().split("\n")[:-1]
+    return [tuple((line.split("\t") + [""])[:2]) for line in lines]
 
 
 def scale_factor(mu: float, lam: float, maxLength: int, modelLength: int, pValue: float) -> float:

@@ -15,7 +15,8 @@
 #include <vector>
 
 struct PhmmModel {
-  std::string name;
+  std::string name;       // NAME
+  std::string accession;  // ACC (optional)
   uint32_t modelLength = 0;  // LENG
   uint32_t maxLength = 0;    // MAXL
   uint32_t alphabetCardinality = 0;

@@ -192,6 +192,7 @@ struct RangeParser {
       case HEADER: {
         const Token& tag = t[0];
         if (tag.is("NAME")) { if (t.size() > 1) cur->name.assign(t[1].p, t[1].n); }
+        else if (tag.is("ACC")) { if (t.size() > 1) cur->accession.assign(t[1].p, t[1].n); }
         else if (tag.is("LENG")) {
           if (t.size() < 2 || !parseUnsigned(t[1], cur->modelLength) || cur->modelLength == 0) fail();
         } else if (tag.is("MAXL")) {
@@ -213,7 +214,7 @@ struct RangeParser {
           cur->matchEmissionScores.assign((size_t)cur->modelLength * cur->alphabetCardinality, 0.f);
           state = SKIP_TRANSITION_LABELS;
         }
-        // every other header tag (ACC, DESC, RF, MM, CONS, CS, MAP, DATE, COM, NSEQ, EFFN, CKSUM, GA, TC, NC, BM, SM)
+        // every other header tag (DESC, RF, MM, CONS, CS, MAP, DATE, COM, NSEQ, EFFN, CKSUM, GA, TC, NC, BM, SM)
         // carries nothing the score table depends on
         break;
       }

@@ -206,6 +206,18 @@ int havac_host_parse_phmm(const char* phmmSrc, float* matchEmissions, uint64_t c
   });
 }
 
+int havac_host_model_names(const char* phmmSrc, char* text, uint64_t cap, uint64_t* nBytes) {
+  if (!phmmSrc || !nBytes) return -1;
+  return guarded(nullptr, [&] {
+    PhmmModels m;
+    m.readP7Hmm(phmmSrc);
+    std::string all;
+    for (const PhmmModel& x : m.models()) all += x.name + "\t" + x.accession + "\n";
+    *nBytes = all.size();
+    if (text && cap >= all.size()) std::memcpy(text, all.data(), all.size());
+  });
+}
+
 float havac_host_scale_factor(float mu, float lambda, uint32_t maxLength, uint32_t modelLength, float pValue) {
   return havacThreshold256ScaleFactor(mu, lambda, maxLength, modelLength, pValue);
 }

@@ -62,6 +62,8 @@ int havac_host_project_phmm(const char* phmmSrc, float pValue, int8_t* table, ui
 /* .hmm -> the match emissions as parsed (negative natural logs, models concatenated, 4 per
  * position), to check the reader's number parsing on its own. */
 int havac_host_parse_phmm(const char* phmmSrc, float* matchEmissions, uint64_t cap, uint64_t* nFloats);
+/* .hmm -> one "NAME<tab>ACC<newline>" line per model, in file order (ACC may be empty). */
+int havac_host_model_names(const char* phmmSrc, char* text, uint64_t cap, uint64_t* nBytes);
 /* findThreshold256ScalingFactor                             PhmmReprojection.cpp:36-66 */
 float havac_host_scale_factor(float mu, float lambda, uint32_t maxLength, uint32_t modelLength, float pValue);
 /* raw u64 hits -> (sequencePosition, sequenceIndex, phmmPosition, phmmIndex); padding hits dropped. */
