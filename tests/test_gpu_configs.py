@@ -83,3 +83,43 @@ def test_config_shape(name, tmp_path):
     if os.path.isdir(out):
         with open(os.path.join(out, "config_sweep.jsonl"), "a") as fh:
             fh.write(json.dumps(line) + "\n")
+
+
+def test_sequence_longer_than_2_32_symbols():
+    """6.5 G symbols (1.6 GB packed; the boundary admits just under 4 GiB, host/HavacHwClient.cpp:92-97):
+    positions, diagonals and segment numbers beyond 32 bits. Fragments of the consensus are planted on
+    both sides of 2^32 and near the end; hits must sit on them, and hit diagonals plus uniformly
+    sampled diagonals must replay exactly on the CPU."""
+    n = 6_500_000_077
+    rows = 257
+    table, cons = synth.consensus_score_table(41, rows)
+    packed = synth.random_packed(41, n)
+    g = synth.rng(41, 3)
+    planted = []
+    for at in [(1 << 32) - 90, (1 << 32) + 5, (1 << 32) + 12288 * 3 - 20, 5_000_000_001, n - 400, 123_456]:
+        a = int(g.integers(0, 60))
+        frag = cons[a:a + 150].copy()
+        mut = g.random(len(frag)) < 0.06
+        frag[mut] = g.integers(0, 4, size=int(mut.sum()))
+        for k, s in enumerate(frag.tolist()):
+            p = at + k
+            packed[p >> 2] = (int(packed[p >> 2]) & ~(3 << (2 * (p & 3)))) | (s << (2 * (p & 3)))
+        planted.append((at, len(frag)))
+    c = HavacHwClient("")
+    try:
+        c.writeSequence(packed)
+        c.writePhmm(table)
+        c.invokeHavacSsvAsync()
+        assert c.waitForHavacSsvAsync() == STATE_COMPLETED
+        hits = c.getHitList()
+        ms = c.deviceTimeMs()
+    finally:
+        c.close()
+    assert np.all(hits[1:] > 0)
+    pos = ((hits >> np.uint64(14)) & np.uint64(0x3ffffff)).astype(np.int64) * 12288 + (hits & np.uint64(0x3fff)).astype(np.int64)
+    assert pos.max() < len(packed) * 4
+    for at, ln in planted:
+        assert ((pos >= at) & (pos < at + ln)).any(), f"no hit on the fragment planted at {at}"
+    assert (pos > (1 << 32)).sum() >= 3
+    checked = O.check_hits_by_replay(packed, table, hits, 300, 2000, seed=41)
+    print(f"6.5 G symbols x {rows} rows: {len(hits)} hits, {n * rows / ms / 1e6:.0f} GCUPS, {checked} diagonals replayed")
