@@ -22,7 +22,10 @@ def build_program():
     build.build_all()
     exe = os.path.join(ROOT, "examples", "havac_benchmark")
     src = exe + ".cpp"
-    if not os.path.exists(exe) or os.path.getmtime(exe) < os.path.getmtime(src):
+    # the program includes the driver's C++ headers (class layouts): rebuild when any of them, or a library, is newer
+    deps = [src, os.path.join(build.LIB, "libhavac_host.so"), os.path.join(build.LIB, "libhavac_cuda.so")]
+    deps += [os.path.join(build.HOST, f) for f in os.listdir(build.HOST) if f.endswith((".hpp", ".h"))]
+    if not os.path.exists(exe) or os.path.getmtime(exe) < max(os.path.getmtime(d) for d in deps):
         subprocess.run(["g++", "-O2", "-std=c++17", src, "-I", build.HOST, "-I", build.INCLUDE, "-L", build.LIB,
                         "-lhavac_host", "-lhavac_cuda", f"-Wl,-rpath,{build.LIB}", "-o", exe], check=True)
     return exe

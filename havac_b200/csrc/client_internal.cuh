@@ -76,5 +76,6 @@ struct havac_cuda_client {
 // sets the client's (or, for c == nullptr, this thread's create-time) error text; returns `code`
 int havac_fail(havac_cuda_client* c, int code, const std::string& msg);
 void havac_free_sequence(DeviceCtx& d);
+int havac_place_sequence(havac_cuda_client* c, const uint8_t* packed, int srcDevice, uint64_t nBytes);
 // hit_postprocess.cu: sorts d.dHits[0, d.hitCount) into the FPGA's emission order on the device
 int havac_sort_hits_on_device(havac_cuda_client* c, DeviceCtx& d);

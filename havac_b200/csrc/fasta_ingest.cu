@@ -500,13 +500,11 @@ int havac_cuda_ingest_fasta(havac_cuda_client* c, const uint8_t* text, uint64_t 
     c->mirrorSymbols = 0;
     return HAVAC_CUDA_OK;
   }
-  // sharded clients take the packed buffer through the ordinary path (halo and ranges handled there)
-  std::vector<uint8_t> host(packedBytes);
-  cudaError_t e = cudaMemcpy(host.data(), dPacked, packedBytes, cudaMemcpyDeviceToHost);
+  // sharded clients: ranges and halos as write_sequence lays them out, copied device to device
+  const int rc = havac_place_sequence(c, (const uint8_t*)dPacked, d.dev, packedBytes);
+  cudaSetDevice(d.dev);
   cudaFree(dPacked);
-  if (e != cudaSuccess) return havac_fail(c, HAVAC_CUDA_E_RUNTIME, std::string("cudaMemcpy: ") + cudaGetErrorString(e));
-  c->d2hBytes += packedBytes;
-  return havac_cuda_write_sequence(c, host.data(), packedBytes);
+  return rc;
 }
 
 int havac_cuda_ingest_records(havac_cuda_client* c, uint64_t* sequenceEnd, uint64_t* headerByteOffset, uint64_t cap, uint64_t* n) {

@@ -117,6 +117,55 @@ void havac_free_sequence(DeviceCtx& d) {
   if (d.dSeq) { cudaSetDevice(d.dev); cudaFree(d.dSeq); d.dSeq = nullptr; d.seqCap = 0; }
 }
 
+// The packed sequence goes to the devices: every device gets its column range plus the resident
+// halo in front of it. The source is a host buffer (srcDevice < 0: write_sequence, blocking like
+// the reference's bo.sync, HavacHwClient.cpp:104) or a buffer on one of this process's GPUs (the
+// device-side FASTA ingest: shards travel by peer copies, nothing through the host).
+int havac_place_sequence(havac_cuda_client* c, const uint8_t* packed, int srcDevice, uint64_t nBytes) {
+  // host/HavacHwClient.cpp:81-97: whole segments only, and strictly less than 4 GiB packed
+  uint64_t nSymbols = nBytes * 4;
+  if (nSymbols % SEG != 0)
+    return fail(c, HAVAC_CUDA_E_LENGTH, "sequence length must be a multiple of the sequence segment length " +
+                                            std::to_string(SEG) + " but sequence of length " + std::to_string(nSymbols) + " was not");
+  if (nBytes >= 4ull * 1024 * 1024 * 1024)
+    return fail(c, HAVAC_CUDA_E_LENGTH, "compressed sequence size must be less than 4GiB. length requested: " +
+                                            std::to_string(nBytes) + " bytes.");
+  if (c->launched && !c->finished) return fail(c, HAVAC_CUDA_E_LOGIC, "a run is in flight");
+  c->seqSegments = nSymbols / SEG;
+  c->mirrorSymbols = 0;
+  uint64_t sb = c->segBegin, se = c->segEnd ? c->segEnd : c->seqSegments;
+  if (se > c->seqSegments) se = c->seqSegments;
+  if (sb > se) sb = se;
+  const uint64_t nSeg = se - sb;
+  const size_t nd = c->devs.size();
+  for (size_t i = 0; i < nd; i++) {
+    DeviceCtx& d = c->devs[i];
+    d.colBegin = (long long)((sb + nSeg * i / nd) * SEG);
+    d.colEnd = (long long)((sb + nSeg * (i + 1) / nd) * SEG);
+    d.resBegin = std::max(0ll, d.colBegin - HALO_RESIDENT) & ~63ll;
+    d.resEnd = d.colEnd;
+    if (d.colEnd <= d.colBegin) { d.resBegin = d.resEnd = d.colBegin; free_sequence(d); continue; }
+    size_t bytes = (size_t)(d.resEnd - d.resBegin) / 4;
+    CK(cudaSetDevice(d.dev));
+    if (bytes != d.seqCap) {  // a reload of the same size (the common case) reuses the allocation
+      free_sequence(d);
+      CK(cudaMalloc(&d.dSeq, bytes));
+      d.seqCap = bytes;
+    }
+    if (srcDevice < 0) {
+      CK(cudaMemcpyAsync(d.dSeq, packed + d.resBegin / 4, bytes, cudaMemcpyHostToDevice, d.stream));
+      c->h2dBytes += bytes;
+    } else {
+      CK(cudaMemcpyPeerAsync(d.dSeq, d.dev, packed + d.resBegin / 4, srcDevice, bytes, d.stream));
+    }
+  }
+  for (DeviceCtx& d : c->devs) {
+    CK(cudaSetDevice(d.dev));
+    CK(cudaStreamSynchronize(d.stream));
+  }
+  return HAVAC_CUDA_OK;
+}
+
 extern "C" {
 
 int havac_cuda_create(const char* deviceSpec, uint32_t deviceIndex, havac_cuda_client** out) {
@@ -212,44 +261,7 @@ int havac_cuda_set_segment_range(havac_cuda_client* c, uint64_t segBegin, uint64
 
 int havac_cuda_write_sequence(havac_cuda_client* c, const uint8_t* packed, uint64_t nBytes) {
   if (!c || (!packed && nBytes)) return HAVAC_CUDA_E_INVALID;
-  // host/HavacHwClient.cpp:81-97: whole segments only, and strictly less than 4 GiB packed
-  uint64_t nSymbols = nBytes * 4;
-  if (nSymbols % SEG != 0)
-    return fail(c, HAVAC_CUDA_E_LENGTH, "sequence length must be a multiple of the sequence segment length " +
-                                            std::to_string(SEG) + " but sequence of length " + std::to_string(nSymbols) + " was not");
-  if (nBytes >= 4ull * 1024 * 1024 * 1024)
-    return fail(c, HAVAC_CUDA_E_LENGTH, "compressed sequence size must be less than 4GiB. length requested: " +
-                                            std::to_string(nBytes) + " bytes.");
-  if (c->launched && !c->finished) return fail(c, HAVAC_CUDA_E_LOGIC, "a run is in flight");
-  c->seqSegments = nSymbols / SEG;
-  c->mirrorSymbols = 0;
-  uint64_t sb = c->segBegin, se = c->segEnd ? c->segEnd : c->seqSegments;
-  if (se > c->seqSegments) se = c->seqSegments;
-  if (sb > se) sb = se;
-  const uint64_t nSeg = se - sb;
-  const size_t nd = c->devs.size();
-  for (size_t i = 0; i < nd; i++) {
-    DeviceCtx& d = c->devs[i];
-    d.colBegin = (long long)((sb + nSeg * i / nd) * SEG);
-    d.colEnd = (long long)((sb + nSeg * (i + 1) / nd) * SEG);
-    d.resBegin = std::max(0ll, d.colBegin - HALO_RESIDENT) & ~63ll;
-    d.resEnd = d.colEnd;
-    if (d.colEnd <= d.colBegin) { d.resBegin = d.resEnd = d.colBegin; free_sequence(d); continue; }
-    size_t bytes = (size_t)(d.resEnd - d.resBegin) / 4;
-    CK(cudaSetDevice(d.dev));
-    if (bytes != d.seqCap) {  // a reload of the same size (the common case) reuses the allocation
-      free_sequence(d);
-      CK(cudaMalloc(&d.dSeq, bytes));
-      d.seqCap = bytes;
-    }
-    CK(cudaMemcpyAsync(d.dSeq, packed + d.resBegin / 4, bytes, cudaMemcpyHostToDevice, d.stream));
-    c->h2dBytes += bytes;
-  }
-  for (DeviceCtx& d : c->devs) {  // the reference's bo.sync is blocking too (HavacHwClient.cpp:104)
-    CK(cudaSetDevice(d.dev));
-    CK(cudaStreamSynchronize(d.stream));
-  }
-  return HAVAC_CUDA_OK;
+  return havac_place_sequence(c, packed, -1, nBytes);
 }
 
 int havac_cuda_write_phmm(havac_cuda_client* c, const int8_t* flat, uint64_t nBytes) {
