@@ -49,6 +49,8 @@ struct havac_cuda_client {
   std::vector<DeviceCtx> devs;
   std::string err;
   unsigned long long hitCap = 16ull << 20;  // per device
+  bool hitCapGrows = true;                  // on overflow the buffers are enlarged and the search repeated
+  int regrowths = 0;                        // how often that happened in the last run
   uint64_t segBegin = 0, segEnd = 0;        // 0,0 = whole buffer
   uint64_t seqSegments = 0;                 // segments in the buffer given to write_sequence
   uint64_t mirrorSymbols = 0;               // N when the resident sequence is the reverse complement over N symbols (strand.cu)

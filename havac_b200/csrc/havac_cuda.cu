@@ -35,14 +35,17 @@ namespace {
 inline int fail(havac_cuda_client* c, int code, const std::string& msg) { return havac_fail(c, code, msg); }
 
 bool parse_spec(const char* spec, uint32_t deviceIndex, int nDev, std::vector<int>& out,
-                unsigned long long& hitCap, std::string& err) {
+                unsigned long long& hitCap, bool& hitCapGrows, std::string& err) {
   std::string s = spec ? spec : "";
   std::string devPart = s;
   size_t semi = s.find(';');
   if (semi != std::string::npos) {
     devPart = s.substr(0, semi);
     std::string opt = s.substr(semi + 1);
-    if (opt.rfind("hitcap=", 0) == 0) hitCap = strtoull(opt.c_str() + 7, nullptr, 10);
+    if (opt.rfind("hitcap=", 0) == 0) {  // "hitcap=N": fixed, overflow is an error; "hitcap=N+": first size, grows
+      hitCap = strtoull(opt.c_str() + 7, nullptr, 10);
+      hitCapGrows = !opt.empty() && opt.back() == '+';
+    }
     if (hitCap == 0) { err = "hitcap must be positive"; return false; }
   }
   if (devPart.rfind("cuda:", 0) != 0) {  // an xclbin path or empty: single device
@@ -82,32 +85,117 @@ void free_table(DeviceCtx& d) {
   d.tabCap = 0;
 }
 
-// Pull the per-device results after the stop events have fired; decides the final state.
-int collect(havac_cuda_client* c) {
-  if (c->finished) return HAVAC_CUDA_OK;
-  float worst = 0.f;
-  bool overflow = false, aborted = false;
+// Queues one search on every device: counters cleared, start event, kernel, stop event.
+int launch_all(havac_cuda_client* c) {
+  c->launches = 0;
   for (DeviceCtx& d : c->devs) {
     CK(cudaSetDevice(d.dev));
-    CK(cudaEventSynchronize(d.evStop));
-    CK(cudaMemcpy(&d.hitCount, d.dHitCount, sizeof d.hitCount, cudaMemcpyDeviceToHost));
-    CK(cudaMemcpy(&d.status, d.dStatus, sizeof d.status, cudaMemcpyDeviceToHost));
-    CK(cudaMemcpy(&d.cycles, d.dCycles, sizeof d.cycles, cudaMemcpyDeviceToHost));
-    c->d2hBytes += sizeof d.hitCount + sizeof d.status;
-    float ms = 0.f;
-    CK(cudaEventElapsedTime(&ms, d.evStart, d.evStop));
-    worst = std::max(worst, ms);
-    overflow |= (d.status & SSV_STATUS_OVERFLOW) != 0 || d.hitCount > c->hitCap;
-    aborted |= (d.status & SSV_STATUS_ABORTED) != 0;
+    d.hitsSorted = false;
+    CK(cudaMemsetAsync(d.dHitCount, 0, sizeof(unsigned long long), d.stream));
+    CK(cudaMemsetAsync(d.dTileCounter, 0, sizeof(unsigned int), d.stream));
+    CK(cudaMemsetAsync(d.dStatus, 0, sizeof(int), d.stream));
+    CK(cudaMemsetAsync(d.dCycles, 0, sizeof(unsigned long long), d.stream));
+    CK(cudaMemsetAsync(d.dAbort, 0, sizeof(int), d.stream));
+    CK(cudaEventRecord(d.evStart, d.stream));
+    if (d.colEnd > d.colBegin) {
+      SsvParams p{};
+      const long long P = c->nRows;
+      long long loadBegin = std::max(d.resBegin, (d.colBegin - (P - 1)) & ~63ll);
+      if (loadBegin < 0) loadBegin = 0;
+      p.seqPacked = d.dSeq + (loadBegin - d.resBegin) / 16;
+      p.nLoad = d.resEnd - loadBegin;
+      p.loadBegin = loadBegin;
+      p.colBegin = d.colBegin;
+      p.colEnd = d.colEnd;
+      p.tab16 = d.dTab16;
+      p.tab8 = d.dTab8;
+      p.nRows = c->nRows;
+      p.rowsPadded = d.rowsPadded;
+      long long dLo = d.colBegin - loadBegin - (P - 1);  // first diagonal that can reach a reported column
+      p.diagBegin = dLo >= 0 ? (dLo & ~63ll) : -((-dLo + 63) & ~63ll);
+      p.nTiles = (uint32_t)((p.nLoad - p.diagBegin + SSV_TILE_DIAGS - 1) / SSV_TILE_DIAGS);
+      p.hits = d.dHits;
+      p.hitCap = c->hitCap;
+      p.hitCount = d.dHitCount;
+      p.tileCounter = d.dTileCounter;
+      p.abortFlag = d.dAbort;
+      p.status = d.dStatus;
+      p.smCycles = d.dCycles;
+      if (c->kernel == KERNEL_SCALAR) ssv_launch_scalar(p, d.stream);
+      else ssv_launch_f16x2(p, d.numSMs, d.stream);
+      CK(cudaGetLastError());
+      c->launches++;
+    }
+    CK(cudaEventRecord(d.evStop, d.stream));
   }
-  c->lastMs = worst;
-  c->finished = true;
-  c->aborted = aborted;
-  if (aborted) c->finalState = HAVAC_CUDA_STATE_ABORT;
-  else if (overflow) {
-    c->finalState = HAVAC_CUDA_STATE_ERROR;
-    c->err = "device hit buffer overflowed (capacity " + std::to_string(c->hitCap) + " hits per device)";
-  } else c->finalState = HAVAC_CUDA_STATE_COMPLETED;
+  return HAVAC_CUDA_OK;
+}
+
+// Enlarges every device's hit buffer to hold `needed` hits (plus slack) if device memory allows.
+bool grow_hit_buffers(havac_cuda_client* c, unsigned long long needed) {
+  const unsigned long long newCap = needed + needed / 8 + 1024;
+  for (DeviceCtx& d : c->devs) {
+    if (cudaSetDevice(d.dev) != cudaSuccess) return false;
+    size_t freeB = 0, totalB = 0;
+    if (cudaMemGetInfo(&freeB, &totalB) != cudaSuccess) return false;
+    // the sort of the hits needs a second buffer of the same size later on
+    if ((double)newCap * 8.0 * 2.2 > (double)freeB + (double)c->hitCap * 8.0) return false;
+  }
+  for (DeviceCtx& d : c->devs) {
+    cudaSetDevice(d.dev);
+    cudaFree(d.dHits);
+    d.dHits = nullptr;
+    if (cudaMalloc(&d.dHits, newCap * sizeof(unsigned long long)) != cudaSuccess) return false;
+  }
+  c->hitCap = newCap;
+  return true;
+}
+
+// Pull the per-device results after the stop events have fired; decides the final state. A hit
+// buffer that overflowed is enlarged to the count the kernel reported and the search repeated
+// (unless the capacity was fixed with ";hitcap=N"): with mayBlock the repeat is waited for here,
+// otherwise the client goes back to "running".
+int collect(havac_cuda_client* c, bool mayBlock = true) {
+  while (!c->finished) {
+    float worst = 0.f;
+    bool overflow = false, aborted = false;
+    unsigned long long most = 0;
+    for (DeviceCtx& d : c->devs) {
+      CK(cudaSetDevice(d.dev));
+      CK(cudaEventSynchronize(d.evStop));
+      CK(cudaMemcpy(&d.hitCount, d.dHitCount, sizeof d.hitCount, cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(&d.status, d.dStatus, sizeof d.status, cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(&d.cycles, d.dCycles, sizeof d.cycles, cudaMemcpyDeviceToHost));
+      c->d2hBytes += sizeof d.hitCount + sizeof d.status;
+      float ms = 0.f;
+      CK(cudaEventElapsedTime(&ms, d.evStart, d.evStop));
+      worst = std::max(worst, ms);
+      overflow |= (d.status & SSV_STATUS_OVERFLOW) != 0 || d.hitCount > c->hitCap;
+      aborted |= (d.status & SSV_STATUS_ABORTED) != 0;
+      most = std::max<unsigned long long>(most, d.hitCount);
+    }
+    c->lastMs += worst;  // a repeated search counts in full
+    if (overflow && !aborted && c->hitCapGrows && c->regrowths < 2) {
+      const unsigned long long before = c->hitCap;
+      if (grow_hit_buffers(c, most)) {
+        c->regrowths++;
+        int rc = launch_all(c);
+        if (rc) return rc;
+        if (!mayBlock) { c->finalState = HAVAC_CUDA_STATE_RUNNING; return HAVAC_CUDA_OK; }
+        continue;
+      }
+      for (DeviceCtx& d : c->devs)  // could not grow: make sure every device still has a buffer
+        if (!d.dHits) { cudaSetDevice(d.dev); cudaMalloc(&d.dHits, before * sizeof(unsigned long long)); c->hitCap = before; }
+    }
+    c->finished = true;
+    c->aborted = aborted;
+    if (aborted) c->finalState = HAVAC_CUDA_STATE_ABORT;
+    else if (overflow) {
+      c->finalState = HAVAC_CUDA_STATE_ERROR;
+      c->err = "device hit buffer overflowed (capacity " + std::to_string(c->hitCap) + " hits per device, " + std::to_string(most) +
+               " needed)";
+    } else c->finalState = HAVAC_CUDA_STATE_COMPLETED;
+  }
   return HAVAC_CUDA_OK;
 }
 
@@ -179,11 +267,13 @@ int havac_cuda_create(const char* deviceSpec, uint32_t deviceIndex, havac_cuda_c
   std::vector<int> ids;
   unsigned long long hitCap = 16ull << 20;
   std::string perr;
-  if (!parse_spec(deviceSpec, deviceIndex, nDev, ids, hitCap, perr)) return fail(nullptr, HAVAC_CUDA_E_NODEVICE, perr);
+  bool hitCapGrows = true;
+  if (!parse_spec(deviceSpec, deviceIndex, nDev, ids, hitCap, hitCapGrows, perr)) return fail(nullptr, HAVAC_CUDA_E_NODEVICE, perr);
 
   havac_cuda_client* c = new (std::nothrow) havac_cuda_client();
   if (!c) return fail(nullptr, HAVAC_CUDA_E_NOMEM, "out of host memory");
   c->hitCap = hitCap;
+  c->hitCapGrows = hitCapGrows;
   auto bail = [&](int code) { g_createError = c->err; havac_cuda_destroy(c); return code; };
   {
     cudaError_t ee = cudaHostAlloc((void**)&c->hostOne, sizeof(int), cudaHostAllocPortable);
@@ -369,47 +459,10 @@ int havac_cuda_invoke_async(havac_cuda_client* c) {
   if (c->seqSegments == 0) return fail(c, HAVAC_CUDA_E_LENGTH, "sequence length in segments cannot be 0, but 0 was given to the client.");
   if (c->nRows == 0) return fail(c, HAVAC_CUDA_E_LENGTH, "phmm length in vectors cannot be 0, but 0 was given to the client.");
   if (c->launched && !c->finished) return fail(c, HAVAC_CUDA_E_LOGIC, "a run is already in flight");
-  c->launches = 0;
-  for (DeviceCtx& d : c->devs) {
-    CK(cudaSetDevice(d.dev));
-    d.hitsSorted = false;
-    CK(cudaMemsetAsync(d.dHitCount, 0, sizeof(unsigned long long), d.stream));
-    CK(cudaMemsetAsync(d.dTileCounter, 0, sizeof(unsigned int), d.stream));
-    CK(cudaMemsetAsync(d.dStatus, 0, sizeof(int), d.stream));
-    CK(cudaMemsetAsync(d.dCycles, 0, sizeof(unsigned long long), d.stream));
-    CK(cudaMemsetAsync(d.dAbort, 0, sizeof(int), d.stream));
-    CK(cudaEventRecord(d.evStart, d.stream));
-    if (d.colEnd > d.colBegin) {
-      SsvParams p{};
-      const long long P = c->nRows;
-      long long loadBegin = std::max(d.resBegin, (d.colBegin - (P - 1)) & ~63ll);
-      if (loadBegin < 0) loadBegin = 0;
-      p.seqPacked = d.dSeq + (loadBegin - d.resBegin) / 16;
-      p.nLoad = d.resEnd - loadBegin;
-      p.loadBegin = loadBegin;
-      p.colBegin = d.colBegin;
-      p.colEnd = d.colEnd;
-      p.tab16 = d.dTab16;
-      p.tab8 = d.dTab8;
-      p.nRows = c->nRows;
-      p.rowsPadded = d.rowsPadded;
-      long long dLo = d.colBegin - loadBegin - (P - 1);  // first diagonal that can reach a reported column
-      p.diagBegin = dLo >= 0 ? (dLo & ~63ll) : -((-dLo + 63) & ~63ll);
-      p.nTiles = (uint32_t)((p.nLoad - p.diagBegin + SSV_TILE_DIAGS - 1) / SSV_TILE_DIAGS);
-      p.hits = d.dHits;
-      p.hitCap = c->hitCap;
-      p.hitCount = d.dHitCount;
-      p.tileCounter = d.dTileCounter;
-      p.abortFlag = d.dAbort;
-      p.status = d.dStatus;
-      p.smCycles = d.dCycles;
-      if (c->kernel == KERNEL_SCALAR) ssv_launch_scalar(p, d.stream);
-      else ssv_launch_f16x2(p, d.numSMs, d.stream);
-      CK(cudaGetLastError());
-      c->launches++;
-    }
-    CK(cudaEventRecord(d.evStop, d.stream));
-  }
+  c->regrowths = 0;
+  c->lastMs = 0.f;
+  int rc = launch_all(c);
+  if (rc) return rc;
   c->launched = true;
   c->finished = false;
   c->aborted = false;
@@ -431,7 +484,7 @@ int havac_cuda_state(havac_cuda_client* c, int* state) {
     if (cudaEventQuery(d.evStart) == cudaSuccess) anyStarted = true;
   }
   if (allDone) {
-    int rc = collect(c);
+    int rc = collect(c, false);
     if (rc) return rc;
     *state = c->finalState;
   } else {

@@ -57,7 +57,11 @@ typedef struct havac_cuda_client havac_cuda_client; /* opaque, one per Havac obj
  * load xclbin, allocate the hit buffers). `deviceSpec` takes the place of the xclbin
  * path: NULL, "" or anything not starting with "cuda:" selects the single GPU
  * `deviceIndex`; "cuda:all" or "cuda:0,1,2" shards the sequence over those GPUs of
- * this process. Optional ";hitcap=<n>" sets the per-device hit capacity. */
+ * this process. The hit buffers start at 16 Mi hits per device and GROW: a run that overflows
+ * them is repeated with buffers sized from the count the kernel reported, so callers see one
+ * completed run (the FPGA design writes past its fixed 3.5 GiB buffer instead,
+ * device/HitReporting.cpp:412). ";hitcap=<n>+" sets the first size; ";hitcap=<n>" (no plus) fixes
+ * the capacity, and an overflow is then reported as E_OVERFLOW. */
 int havac_cuda_create(const char* deviceSpec, uint32_t deviceIndex, havac_cuda_client** out);
 int havac_cuda_destroy(havac_cuda_client* c);
 

@@ -136,6 +136,39 @@ def test_hit_buffer_overflow_is_reported_not_silent():
         c.close()
 
 
+def test_hit_buffer_grows_and_the_search_repeats():
+    """Without a fixed capacity (";hitcap=N+" sets only the first size) an overflowed run enlarges the
+    buffers to the count the kernel reported and searches again; callers see one completed run, by
+    blocking wait and by polling."""
+    import time
+    from havac_b200.client import STATE_COMPLETED
+    g = synth.rng(74, 1)
+    table = g.integers(-10, 70, size=(200, 4)).astype(np.int8)  # positive drift: hits everywhere
+    packed = synth.random_packed(74, 12288 * 8)
+    pos, row = O.soft_ssv(synth.unpack_2bit(packed), table, cap=1 << 24)
+    want = np.sort(O.encode_hits(pos, row))
+    assert len(want) > 3000
+    for poll in (False, True):
+        c = HavacHwClient(";hitcap=1000+")
+        try:
+            c.writeSequence(packed)
+            c.writePhmm(table)
+            c.invokeHavacSsvAsync()
+            if poll:
+                deadline = time.time() + 60
+                while c.getHwState() != STATE_COMPLETED:
+                    assert time.time() < deadline
+                    time.sleep(0.001)
+            else:
+                assert c.waitForHavacSsvAsync() == STATE_COMPLETED
+            assert np.array_equal(np.sort(c.getHitList()), want)
+            c.invokeHavacSsvAsync()  # the enlarged buffer serves the next run at once
+            assert c.waitForHavacSsvAsync() == STATE_COMPLETED
+            assert np.array_equal(np.sort(c.getHitList()), want)
+        finally:
+            c.close()
+
+
 def test_full_size_properties_c2():
     """BASELINE configs[1] size (100 Mbp x ~35 k rows), where brute force on the CPU is impossible:
     (1) every GPU hit replays to a hit at exactly that row on its diagonal (no false positives),
