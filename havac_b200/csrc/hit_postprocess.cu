@@ -14,6 +14,9 @@
 
 #include <algorithm>
 #include <string>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <vector>
 
 #include "client_internal.cuh"
@@ -241,11 +244,16 @@ extern "C" int havac_cuda_resolve_hits(havac_cuda_client* c, const uint64_t* seq
     acc += modelLength[i];
   }
   uint64_t kept = 0;
+  const bool trace = std::getenv("HAVAC_TRACE") != nullptr;
+  auto now = [] { return std::chrono::steady_clock::now(); };
+  auto secs = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double>(b - a).count(); };
   for (DeviceCtx& d : c->devs) {  // devices hold increasing segment ranges: device order is emission order
     const unsigned long long n = d.hitCount;
     if (!n) continue;
+    const auto t0 = now();
     rc = havac_sort_hits_on_device(c, d);
     if (rc) return rc;
+    const auto t1 = now();
     CK(cudaSetDevice(d.dev));
     Frees frees;
     auto dalloc = [&](void** p, size_t bytes) {
@@ -273,6 +281,7 @@ extern "C" int havac_cuda_resolve_hits(havac_cuda_client* c, const uint64_t* seq
     CK(cudaMemcpyAsync(phmmPosition + kept, dPhmmPos, n * 4, cudaMemcpyDeviceToHost, d.stream));
     CK(cudaMemcpyAsync(phmmIndex + kept, dPhmmIdx, n * 4, cudaMemcpyDeviceToHost, d.stream));
     CK(cudaStreamSynchronize(d.stream));
+    const auto t2 = now();
     c->h2dBytes += nSequences * 8 + (uint64_t)nModels * 4;
     c->d2hBytes += n * 20;
     uint64_t w = kept;
@@ -287,6 +296,9 @@ extern "C" int havac_cuda_resolve_hits(havac_cuda_client* c, const uint64_t* seq
       w++;
     }
     kept = w;
+    if (trace)
+      std::fprintf(stderr, "[havac trace] device %d: %llu hits, sort %.3f s, resolve + copy back %.3f s, squeeze %.3f s\n", d.dev, n,
+                   secs(t0, t1), secs(t1, t2), secs(t2, now()));
   }
   *nOut = kept;
   return HAVAC_CUDA_OK;

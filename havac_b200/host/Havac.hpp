@@ -36,6 +36,7 @@ const std::string xclbinSrcDefault = "../device/bin/havac.xclbin";
 class HavacHit {
 public:
   HavacHit(const uint64_t sequencePosition, const uint32_t sequenceIndex, const uint32_t phmmPosition, const uint32_t phmmIndex);
+  HavacHit() {}  // an addition: leaves the fields unset, so that a vector of hits can be sized first and filled by several threads
   uint64_t sequencePosition;
   uint32_t sequenceIndex;
   uint32_t phmmPosition;

@@ -5,6 +5,10 @@
 //   allocation failure     -> std::bad_alloc
 #include "HavacHwClient.hpp"
 
+#include <utility>
+#include <initializer_list>
+#include <thread>
+#include <algorithm>
 #include <cstdio>
 #include <new>
 #include <stdexcept>
@@ -119,26 +123,44 @@ void HavacHwClient::reverseComplement(uint64_t nSymbols) {
   check(havac_cuda_reverse_complement(handle, nSymbols), "reverseComplement");
 }
 
-void HavacHwClient::resolveHits(const std::vector<uint64_t>& sequenceEndPositions, const std::vector<uint32_t>& modelLengths,
-                                std::vector<uint64_t>& sequencePosition, std::vector<uint32_t>& sequenceIndex,
-                                std::vector<uint32_t>& phmmPosition, std::vector<uint32_t>& phmmIndex) {
+namespace {
+// first write to every page of [p, p + bytes), spread over threads
+void touchPages(std::initializer_list<std::pair<void*, size_t>> ranges) {
+  const unsigned threads = std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+  for (const auto& r : ranges) {
+    char* p = (char*)r.first;
+    const size_t bytes = r.second;
+    if (bytes < (64u << 20) || threads == 1) continue;  // small arrays: the copy itself touches them
+    std::vector<std::thread> pool;
+    const size_t slice = (bytes / threads + 4095) & ~(size_t)4095;
+    for (unsigned t = 0; t < threads; t++)
+      pool.emplace_back([=] {
+        const size_t a = (size_t)t * slice, b = std::min(bytes, a + slice);
+        for (size_t k = a; k < b; k += 4096) p[k] = 0;
+      });
+    for (std::thread& th : pool) th.join();
+  }
+}
+}  // namespace
+
+HavacHwClient::ResolvedHits HavacHwClient::resolveHits(const std::vector<uint64_t>& sequenceEndPositions,
+                                                       const std::vector<uint32_t>& modelLengths) {
   uint64_t n = 0;
   check(havac_cuda_num_hits(handle, &n), "getHitList");
   std::printf("client reported %llu hits\n", (unsigned long long)n);  // HavacHwClient.cpp:189
-  sequencePosition.resize(n);
-  sequenceIndex.resize(n);
-  phmmPosition.resize(n);
-  phmmIndex.resize(n);
-  uint64_t kept = 0;
-  if (n)
-    check(havac_cuda_resolve_hits(handle, sequenceEndPositions.data(), sequenceEndPositions.size(), modelLengths.data(),
-                                  (uint32_t)modelLengths.size(), sequencePosition.data(), sequenceIndex.data(),
-                                  phmmPosition.data(), phmmIndex.data(), n, &kept),
-          "getHitsFromFinishedRun");
-  sequencePosition.resize(kept);
-  sequenceIndex.resize(kept);
-  phmmPosition.resize(kept);
-  phmmIndex.resize(kept);
+  ResolvedHits out;
+  if (n == 0) return out;
+  out.sequencePosition.reset(new uint64_t[n]);
+  out.sequenceIndex.reset(new uint32_t[n]);
+  out.phmmPosition.reset(new uint32_t[n]);
+  out.phmmIndex.reset(new uint32_t[n]);
+  touchPages({{out.sequencePosition.get(), n * 8}, {out.sequenceIndex.get(), n * 4}, {out.phmmPosition.get(), n * 4},
+              {out.phmmIndex.get(), n * 4}});
+  check(havac_cuda_resolve_hits(handle, sequenceEndPositions.data(), sequenceEndPositions.size(), modelLengths.data(),
+                                (uint32_t)modelLengths.size(), out.sequencePosition.get(), out.sequenceIndex.get(),
+                                out.phmmPosition.get(), out.phmmIndex.get(), n, &out.count),
+        "getHitsFromFinishedRun");
+  return out;
 }
 
 void HavacHwClient::setSegmentRange(uint64_t segBegin, uint64_t segEnd) {

@@ -59,10 +59,15 @@ public:
   // resident sequence <-> its reverse complement over the first nSymbols symbols (havac_cuda_reverse_complement)
   void reverseComplement(uint64_t nSymbols);
   // Hits of the finished run, sorted and resolved on the device (havac_cuda_resolve_hits): four
-  // parallel arrays in emission order, padding hits dropped.
-  void resolveHits(const std::vector<uint64_t>& sequenceEndPositions, const std::vector<uint32_t>& modelLengths,
-                   std::vector<uint64_t>& sequencePosition, std::vector<uint32_t>& sequenceIndex,
-                   std::vector<uint32_t>& phmmPosition, std::vector<uint32_t>& phmmIndex);
+  // parallel arrays in emission order, padding hits dropped. The arrays are allocated without
+  // being zeroed and their pages are first touched by several threads: at 10^8 hits the page
+  // faults of a plain vector resize cost more than the device work.
+  struct ResolvedHits {
+    std::unique_ptr<uint64_t[]> sequencePosition;
+    std::unique_ptr<uint32_t[]> sequenceIndex, phmmPosition, phmmIndex;
+    uint64_t count = 0;
+  };
+  ResolvedHits resolveHits(const std::vector<uint64_t>& sequenceEndPositions, const std::vector<uint32_t>& modelLengths);
 
   // harness helpers (no reference counterpart)
   void setSegmentRange(uint64_t segBegin, uint64_t segEnd);
