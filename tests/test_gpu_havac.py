@@ -169,6 +169,43 @@ def test_hit_buffer_grows_and_the_search_repeats():
             c.close()
 
 
+def test_two_clients_on_one_gpu_run_side_by_side():
+    """Two Havac objects alive at once (the library keeps no process-wide state): different inputs,
+    runs in flight at the same time from two threads, each gets its own hits."""
+    import threading
+    cases = []
+    for seed, rows, n in ((81, 300, 2_000_000), (82, 777, 1_500_000)):
+        table, cons = synth.consensus_score_table(seed, rows)
+        sym = synth.random_symbols(seed, n)
+        synth.plant_consensus(seed, sym, cons, copies=20, substitution=0.08)
+        packed = synth.pack_2bit(sym)
+        pos, row = O.soft_ssv(synth.unpack_2bit(packed), table)
+        cases.append((packed, table, np.sort(O.encode_hits(pos, row))))
+    clients = [HavacHwClient("") for _ in cases]
+    got = [None, None]
+    try:
+        for c, (packed, table, _) in zip(clients, cases):
+            c.writeSequence(packed)
+            c.writePhmm(table)
+
+        def work(i):
+            for _ in range(3):
+                clients[i].invokeHavacSsvAsync()
+                assert clients[i].waitForHavacSsvAsync() == STATE_COMPLETED
+                got[i] = np.sort(clients[i].getHitList())
+
+        threads = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+    finally:
+        for c in clients:
+            c.close()
+    for g, (_, _, want) in zip(got, cases):
+        assert len(want) >= 20 and np.array_equal(g, want)
+
+
 def test_full_size_properties_c2():
     """BASELINE configs[1] size (100 Mbp x ~35 k rows), where brute force on the CPU is impossible:
     (1) every GPU hit replays to a hit at exactly that row on its diagonal (no false positives),
