@@ -12,11 +12,12 @@ def main():
     n = int(float(sys.argv[1])) if len(sys.argv) > 1 else 100_000_000
     rows = int(float(sys.argv[2])) if len(sys.argv) > 2 else 35_000
     reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
+    pos_lo = int(sys.argv[4]) if len(sys.argv) > 4 else 14  # consensus scores pos_lo..pos_lo+8: raise for denser hits
     g = synth.rng(99, 1)
     t = g.integers(-32, -8, size=(rows, 4)).astype(np.int8)
-    t[np.arange(rows), g.integers(0, 4, size=rows)] = g.integers(14, 23, size=rows)
+    t[np.arange(rows), g.integers(0, 4, size=rows)] = g.integers(pos_lo, pos_lo + 9, size=rows)
     packed = synth.random_packed(99, n)
-    c = HavacHwClient("")
+    c = HavacHwClient(";hitcap=200000000+")
     c.writeSequence(packed); c.writePhmm(t)
     for i in range(reps):
         t0 = time.time(); c.invokeHavacSsvAsync(); st = c.waitForHavacSsvAsync(); wall = time.time() - t0
