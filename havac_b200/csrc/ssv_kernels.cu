@@ -321,27 +321,33 @@ __device__ __forceinline__ void emit_hit_active(const SsvParams& prm, long long 
 // 256 (s + e) rounds to +inf exactly when s + e >= 256, so "inf" IS the hit test of
 // SoftSsv.cpp:44 / HavacHls.cpp:386, and the half that hit is reset to 0 as the reference does.
 // Lanes and registers with nothing to do skip; no warp-synchronous call is made in here.
-//   w    : fast-path result; replayed registers are overwritten with the exact state
+//   infMask : bit k set = the caller's register k holds an inf after the fast path
 //   edge : the tile still has diagonals left of column 0 in this superblock. Registers wholly
 //          left of it are zeroed (nothing real yet: prev score is 0 at column 0, SoftSsv.cpp:37),
 //          registers crossing it are replayed with the cells left of column 0 held at 0.
-__device__ __noinline__ void exact_rows(const SsvParams& prm, const FastSmem& sm, const uint2* tab,
-                                        uint32_t (&w)[R], bool edge, long long d0, long long D0,
-                                        uint32_t pb, uint32_t nRowsReplay) {
-  const uint32_t* ck = reinterpret_cast<const uint32_t*>(&sm.ckpt[0][0]);
+__device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, FastSmem& sm, const uint2* tab, uint32_t infMask, bool edge,
+                                            long long d0, long long D0, uint32_t pb, uint32_t nRowsReplay) {
+  // Registers do not cross this call: the caller says which of its registers hold an inf
+  // (infMask), the exact end state of every replayed register is written over its checkpoint
+  // slot, and the returned mask tells the caller which slots to read back.
+  uint32_t* ck = reinterpret_cast<uint32_t*>(&sm.ckpt[0][0]);
+  uint32_t changed = 0;
 #pragma unroll 1
-  for (int k = 0; k < R; k++) {
+  for (uint32_t todo = edge ? 0xffffu : infMask; todo; todo &= todo - 1) {
+    const int k = __ffs(todo) - 1;
+    uint32_t* slot = &ck[((k >> 2) * THREADS + threadIdx.x) * 4 + (k & 3)];
     const long long dlo = d0 + 2 * k;  // diagonals dlo (low half) and dlo + 1 (high half)
     bool crossing = false;
     if (edge) {
       if (dlo + 1 + (long long)pb + nRowsReplay - 1 < 0) {  // wholly left of column 0
-        w[k] = 0u;
+        *slot = 0u;
+        changed |= 1u << k;
         continue;
       }
       crossing = dlo + (long long)pb < 0;
     }
-    if (!crossing && !has_inf(w[k])) continue;
-    uint32_t v = ck[((k >> 2) * THREADS + threadIdx.x) * 4 + (k & 3)];
+    if (!crossing && !((infMask >> k) & 1u)) continue;
+    uint32_t v = *slot;
     const uint32_t s0 = (uint32_t)(dlo + (long long)pb - D0);  // ring offset of the low half's symbol at row pb
     // Sixteen rows at a time are first run without looking (loads and lookups independent of the
     // state, so they pipeline; the chain is one HFMA2 per row): only the sixteen that end in inf
@@ -389,8 +395,10 @@ __device__ __noinline__ void exact_rows(const SsvParams& prm, const FastSmem& sm
         }
       }
     }
-    w[k] = v;
+    *slot = v;
+    changed |= 1u << k;
   }
+  return changed;
 }
 
 // One 4-row group of the fast path. U = group index inside the 32-row block (compile time),
@@ -544,13 +552,15 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_kernel(const
         for (int k = 0; k < R; k += 2) mx = __vimax3_s16x2(mx, w[k], w[k + 1]);
         const bool edge = D0 + (long long)pb < 0;  // tile-uniform: diagonals left of column 0 remain
         if (edge || __any_sync(FULL, has_inf(mx))) {
-          // cold path: hand a copy to the out-of-line replay so w stays in registers above
-          uint32_t wc[R];
+          // cold path, out of line: the replay leaves the exact states in the checkpoint slots
+          uint32_t infMask = 0;
 #pragma unroll
-          for (int k = 0; k < R; k++) wc[k] = w[k];
-          exact_rows(prm, sm, sm.tab[buf], wc, edge, d0, D0, pb, rows);
+          for (int k = 0; k < R; k++) infMask |= has_inf(w[k]) ? (1u << k) : 0u;
+          const uint32_t changed = exact_rows(prm, sm, sm.tab[buf], infMask, edge, d0, D0, pb, rows);
+          const uint32_t* ck = reinterpret_cast<const uint32_t*>(&sm.ckpt[0][0]);
 #pragma unroll
-          for (int k = 0; k < R; k++) w[k] = wc[k];
+          for (int k = 0; k < R; k++)
+            if ((changed >> k) & 1u) w[k] = ck[((k >> 2) * THREADS + tid) * 4 + (k & 3)];
         }
       }
 
