@@ -325,43 +325,85 @@ __device__ __forceinline__ void emit_hit_active(const SsvParams& prm, long long 
 //   edge : the tile still has diagonals left of column 0 in this superblock. Registers wholly
 //          left of it are zeroed (nothing real yet: prev score is 0 at column 0, SoftSsv.cpp:37),
 //          registers crossing it are replayed with the cells left of column 0 held at 0.
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint2 lds_v2(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+  return v;
+}
+
+// A register whose fp16 halves just reached inf at row p: report the hit(s), reset those halves
+// to 0 as the reference does (SoftSsv.cpp:44-49), return the register.
+__device__ __noinline__ uint32_t on_hit(const SsvParams& prm, uint32_t v, long long dlo, uint32_t p) {
+#pragma unroll 1
+  for (int h = 0; h < 2; h++) {
+    if (((v >> (16 * h)) & 0xffffu) != 0x7c00u) continue;
+    v &= h ? 0x0000ffffu : 0xffff0000u;
+    const long long col = dlo + h + (long long)p + prm.loadBegin;
+    if (p < prm.nRows && col >= prm.colBegin && col < prm.colEnd) emit_hit_active(prm, col, p);
+  }
+  return v;
+}
+
 __device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, FastSmem& sm, const uint2* tab, uint32_t infMask, bool edge,
                                             long long d0, long long D0, uint32_t pb, uint32_t nRowsReplay) {
   // Registers do not cross this call: the caller says which of its registers hold an inf
   // (infMask), the exact end state of every replayed register is written over its checkpoint
-  // slot, and the returned mask tells the caller which slots to read back.
-  uint32_t* ck = reinterpret_cast<uint32_t*>(&sm.ckpt[0][0]);
+  // slot, and the returned mask tells the caller which slots to read back. Shared memory is read
+  // with shared-space addresses (a generic pointer would cost an address translation per load).
+  const uint32_t ckBase = smem_u32(&sm.ckpt[0][0]), ringBase = smem_u32(&sm.ring[0][0]), tabBase = smem_u32(tab);
   uint32_t changed = 0;
 #pragma unroll 1
   for (uint32_t todo = edge ? 0xffffu : infMask; todo; todo &= todo - 1) {
     const int k = __ffs(todo) - 1;
-    uint32_t* slot = &ck[((k >> 2) * THREADS + threadIdx.x) * 4 + (k & 3)];
+    const uint32_t slot = ckBase + 4u * (uint32_t)(((k >> 2) * THREADS + threadIdx.x) * 4 + (k & 3));
     const long long dlo = d0 + 2 * k;  // diagonals dlo (low half) and dlo + 1 (high half)
     bool crossing = false;
     if (edge) {
       if (dlo + 1 + (long long)pb + nRowsReplay - 1 < 0) {  // wholly left of column 0
-        *slot = 0u;
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(slot), "r"(0u) : "memory");
         changed |= 1u << k;
         continue;
       }
       crossing = dlo + (long long)pb < 0;
     }
     if (!crossing && !((infMask >> k) & 1u)) continue;
-    uint32_t v = *slot;
+    uint32_t v = lds_u32(slot);
     const uint32_t s0 = (uint32_t)(dlo + (long long)pb - D0);  // ring offset of the low half's symbol at row pb
-    // Sixteen rows at a time are first run without looking (loads and lookups independent of the
-    // state, so they pipeline; the chain is one HFMA2 per row): only the sixteen that end in inf
-    // are walked row by row below. nRowsReplay is a multiple of 32.
+    if (crossing) {
+      // first tiles only: row by row, with the cells left of column 0 held at 0
 #pragma unroll 1
-    for (uint32_t rb = 0; rb < nRowsReplay; rb += 16) {
-      if (!crossing) {
+      for (uint32_t r = 0; r < nRowsReplay; r++) {
+        const uint32_t sy = s0 + r, p = pb + r;
+        const uint32_t sel = lds_u32(ringBase + (((sy & 31u) >> 2) * (uint32_t)NSLOT + (sy >> 5) % (uint32_t)NSLOT) * 16u + (sy & 3u) * 4u);
+        const uint2 e2 = lds_v2(tabBase + (p & (TC - 1)) * 8u);
+        v = hfma2_relu_add(prmt(e2.x, e2.y, sel), v);
+        const long long j = dlo + (long long)p;
+        if (j < 0) v &= 0xffff0000u;
+        if (j + 1 < 0) v = 0u;
+        if (has_inf(v)) v = on_hit(prm, v, dlo, p);
+      }
+    } else {
+      // Sixteen rows at a time: the lookups do not depend on the state, so their loads pipeline,
+      // and the chain is one HFMA2 per row. The sixteen are first run without looking; only if
+      // they end in inf are they walked again, from the same looked-up values, one row at a time.
+      // nRowsReplay is a multiple of 32.
+#pragma unroll 1
+      for (uint32_t rb = 0; rb < nRowsReplay; rb += 16) {
+        const uint32_t sA = s0 + rb, qA = sA >> 5;
+        const uint32_t slotA = qA % (uint32_t)NSLOT, slotB = slotA + 1 == (uint32_t)NSLOT ? 0u : slotA + 1;
         uint32_t m[16];
 #pragma unroll
         for (uint32_t i = 0; i < 16; i++) {
-          const uint32_t s = s0 + rb + i;
-          const uint32_t* words = reinterpret_cast<const uint32_t*>(&sm.ring[(s & 31u) >> 2][(s >> 5) % (uint32_t)NSLOT]);
-          const uint2 e2 = tab[(pb + rb + i) & (TC - 1)];
-          m[i] = prmt(e2.x, e2.y, words[s & 3u]);
+          const uint32_t sy = sA + i;
+          const uint32_t sl = (sy >> 5) == qA ? slotA : slotB;
+          const uint32_t sel = lds_u32(ringBase + (((sy & 31u) >> 2) * (uint32_t)NSLOT + sl) * 16u + (sy & 3u) * 4u);
+          const uint2 e2 = lds_v2(tabBase + ((pb + rb + i) & (TC - 1)) * 8u);
+          m[i] = prmt(e2.x, e2.y, sel);
         }
         uint32_t vv = v;
 #pragma unroll
@@ -370,32 +412,14 @@ __device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, FastSmem& sm, 
           v = vv;
           continue;
         }
-      }
-#pragma unroll 4
-      for (uint32_t r = rb; r < rb + 16; r++) {
-        const uint32_t s = s0 + r;
-        const uint32_t* words = reinterpret_cast<const uint32_t*>(&sm.ring[(s & 31u) >> 2][(s >> 5) % (uint32_t)NSLOT]);
-        const uint32_t sel = words[s & 3u];
-        const uint32_t p = pb + r;
-        const uint2 e2 = tab[p & (TC - 1)];
-        v = hfma2_relu_add(prmt(e2.x, e2.y, sel), v);
-        if (crossing) {  // cells left of column 0 do not exist
-          const long long j = dlo + (long long)p;
-          if (j < 0) v &= 0xffff0000u;
-          if (j + 1 < 0) v = 0u;
-        }
-        if (has_inf(v)) {
-#pragma unroll 1
-          for (int h = 0; h < 2; h++) {
-            if (((v >> (16 * h)) & 0xffffu) != 0x7c00u) continue;
-            v &= h ? 0x0000ffffu : 0xffff0000u;
-            const long long col = dlo + h + (long long)p + prm.loadBegin;
-            if (p < prm.nRows && col >= prm.colBegin && col < prm.colEnd) emit_hit_active(prm, col, p);
-          }
+#pragma unroll
+        for (uint32_t i = 0; i < 16; i++) {
+          v = hfma2_relu_add(m[i], v);
+          if (has_inf(v)) v = on_hit(prm, v, dlo, pb + rb + i);
         }
       }
     }
-    *slot = v;
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(slot), "r"(v) : "memory");
     changed |= 1u << k;
   }
   return changed;
