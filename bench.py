@@ -219,7 +219,13 @@ def run_gpu(args, rank, world, local_rank):
         raise SystemExit("bench.py: no CUDA device; the SSV path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dist = None
+    stdout_fd = None
     if world > 1:
+        # NCCL writes its version banner to file descriptor 1; stdout must carry the one JSON line
+        # only, so everything below goes to stderr until rank 0 prints the result
+        sys.stdout.flush()
+        stdout_fd = os.dup(1)
+        os.dup2(2, 1)
         import torch.distributed as dist  # noqa: F811
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -365,7 +371,12 @@ def run_gpu(args, rank, world, local_rank):
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "published_fpga_gcups": PUBLISHED_FPGA_GCUPS,
         }
+        if stdout_fd is not None:
+            sys.stdout.flush()
+            os.dup2(stdout_fd, 1)
         print(json.dumps(out), flush=True)
+        if stdout_fd is not None:
+            os.dup2(2, 1)  # whatever the teardown prints goes to stderr too
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
