@@ -166,10 +166,11 @@ def run_reference(args, rank):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    packed, table, n, lengths = build_workload(1)
+    packed, table, n, lengths = build_workload(max(1, args.gpus))  # the arm's own workload at this N
     rows_total = table.shape[0]
-    # bounded sample: 4 Mbp x the first 8000 rows of the same table per step (~10 s on 16-24 cores)
-    n_s, rows_s = 4_000_000, min(8000, rows_total)
+    # bounded sample: 250 k symbols per host thread (4 Mbp on 16 threads) x the first 8000 rows of the same
+    # table per step, ~8 s a step whatever the core count, so the default 13 steps end within two minutes
+    n_s, rows_s = 250_000 * threads, min(8000, rows_total)
     vals = []
     for i in range(args.warmup + args.steps):
         g, kind, dt, nh = cpu_ssv_rate(packed, table, n_s, rows_s, threads, 0)
@@ -183,7 +184,7 @@ def run_reference(args, rank):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": value / PUBLISHED_FPGA_GCUPS, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": workload_name(1, rows_total), "sample": sample},
+        "config": {"workload": workload_name(max(1, args.gpus), rows_total), "sample": sample},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
