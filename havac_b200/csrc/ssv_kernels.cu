@@ -466,7 +466,27 @@ struct RowGroups<BLOCK_ROWS / 4> {
                                              const uint2*, const uint4*) {}
 };
 
-__global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_kernel(const SsvParams prm) {
+// The first END groups of a block only: the last block of a tile's rows when the table does not
+// end on a 32-row boundary (a 200-row model would otherwise pay for 224 rows). Nothing runs after
+// it in the tile, so the window registers it leaves half rotated are never used again.
+template <int U, int END>
+struct RowGroupsTo {
+  static __device__ __forceinline__ void run(uint32_t (&w)[R], uint32_t (&e0)[R], uint32_t (&e1)[R],
+                                             const uint2* tabRow, const uint4* ringSlot) {
+    four_rows<U>(w, e0, e1, tabRow, ringSlot);
+    RowGroupsTo<U + 1, END>::run(w, e0, e1, tabRow, ringSlot);
+  }
+};
+template <int END>
+struct RowGroupsTo<END, END> {
+  static __device__ __forceinline__ void run(uint32_t (&)[R], uint32_t (&)[R], uint32_t (&)[R],
+                                             const uint2*, const uint4*) {}
+};
+
+// TAIL = the build for short tables, where a partial last block is worth a branch per block; the
+// plain build keeps the hot loop exactly as it was measured (the branch cost 2 % at 35 k rows).
+template <bool TAIL>
+__device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
   extern __shared__ __align__(16) unsigned char smemRaw[];
   FastSmem& sm = *reinterpret_cast<FastSmem*>(smemRaw);
   const int tid = threadIdx.x;
@@ -565,7 +585,15 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_kernel(const
         const uint2* tabRow = sm.tab[buf] + (pb & (TC - 1));
 #pragma unroll 1
         for (int b = 0; b < nb; b++) {
-          RowGroups<0>::run(w, e0, e1, tabRow + b * BLOCK_ROWS, &sm.ring[0][g]);
+          if constexpr (TAIL) {
+            const int left = (int)(chunkEnd - (long long)pb) - b * BLOCK_ROWS;  // rows of the tile from this block on
+            if (left > 24) RowGroups<0>::run(w, e0, e1, tabRow + b * BLOCK_ROWS, &sm.ring[0][g]);
+            else if (left > 16) RowGroupsTo<0, 6>::run(w, e0, e1, tabRow + b * BLOCK_ROWS, &sm.ring[0][g]);
+            else if (left > 8) RowGroupsTo<0, 4>::run(w, e0, e1, tabRow + b * BLOCK_ROWS, &sm.ring[0][g]);
+            else RowGroupsTo<0, 2>::run(w, e0, e1, tabRow + b * BLOCK_ROWS, &sm.ring[0][g]);
+          } else {
+            RowGroups<0>::run(w, e0, e1, tabRow + b * BLOCK_ROWS, &sm.ring[0][g]);
+          }
           g = (g + 1 == (uint32_t)NSLOT) ? 0u : g + 1;
         }
 
@@ -608,6 +636,14 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_kernel(const
   if (tid == 0 && blockIdx.x == 0) *prm.smCycles = (unsigned long long)(clock64() - clk0);
 }
 
+__global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_kernel(const SsvParams prm) {
+  ssv_f16x2_body<false>(prm);
+}
+// Short tables that end 1..24 rows into their last block (chosen in ssv_launch_f16x2).
+__global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_tail_kernel(const SsvParams prm) {
+  ssv_f16x2_body<true>(prm);
+}
+
 }  // namespace
 
 // =======================================================================================
@@ -631,9 +667,12 @@ static bool f16x2_prepare() {
   static int done = -1;  // per process; every device of this process runs the same image
   int dev = 0;
   cudaGetDevice(&dev);
-  cudaError_t e = cudaFuncSetAttribute(ssv_f16x2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem));
-  if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(ssv_f16x2_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  cudaError_t e = cudaSuccess;
+  for (auto kernel : {ssv_f16x2_kernel, ssv_f16x2_tail_kernel}) {
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  }
   done = (e == cudaSuccess);
   return done == 1;
 }
@@ -649,7 +688,17 @@ void ssv_launch_f16x2(const SsvParams& prm, int numSMs, void* stream) {
   int grid = numSMs * ssv_f16x2_ctas_per_sm();
   if ((unsigned)grid > prm.nTiles) grid = (int)prm.nTiles;
   if (grid < 1) grid = 1;
-  ssv_f16x2_kernel<<<grid, THREADS, sizeof(FastSmem), (cudaStream_t)stream>>>(prm);
+  // A table that ends 1..24 rows into its last 32-row block can skip the 8, 16 or 24 rows it does not
+  // have, at the price of the tail build's hot loop (a branch per block: 2 % slower, measured). It is
+  // taken where the rows saved are at least 1/32 of the table: 72 rows +20 %, 200 rows +7.6 %,
+  // 1000 rows break-even (plain), 2040 rows would lose 1.4 % (plain).
+  const uint32_t tailRows = prm.nRows % BLOCK_ROWS;
+  const uint32_t saved = tailRows ? BLOCK_ROWS - ((tailRows + 7u) & ~7u) : 0u;
+  const uint32_t padded = (prm.nRows + BLOCK_ROWS - 1) / BLOCK_ROWS * BLOCK_ROWS;
+  if (saved != 0 && saved * 32u >= padded)
+    ssv_f16x2_tail_kernel<<<grid, THREADS, sizeof(FastSmem), (cudaStream_t)stream>>>(prm);
+  else
+    ssv_f16x2_kernel<<<grid, THREADS, sizeof(FastSmem), (cudaStream_t)stream>>>(prm);
 }
 
 void ssv_launch_scalar(const SsvParams& prm, void* stream) {

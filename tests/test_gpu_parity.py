@@ -164,3 +164,18 @@ def test_all_gpus_of_the_box_in_one_process():
     many = gpu_hits(packed, table, spec="cuda:all")
     assert len(one) > 20 and np.array_equal(one, many)
     assert np.array_equal(np.sort(one), oracle_hits(packed, table))
+
+
+def test_every_tail_length():
+    """Tables ending 1..32 rows into their last 32-row block (short tables run a build of the fast path
+    that computes 8, 16, 24 or 32 rows of it), hit-dense so that hits fall in the last rows."""
+    g = synth.rng(9, 1)
+    full = g.integers(-20, 60, size=(96, 4)).astype(np.int8)
+    packed = synth.pack_2bit(synth.random_symbols(9, 2 * 12_288))
+    for rows in range(33, 97):
+        t = np.ascontiguousarray(full[:rows])
+        t[-1, :] = 60  # whatever a diagonal holds above 195 hits in the last row
+        want = oracle_hits(packed, t)
+        assert (want >> np.uint64(40)).max() == rows - 1, "no hit in the last row: the case would prove nothing"
+        got = np.sort(gpu_hits(packed, t, "f16x2"))
+        assert np.array_equal(got, want), f"rows={rows}: {len(got)} hits vs oracle {len(want)}"
