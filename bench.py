@@ -22,7 +22,17 @@ data path; torch.distributed only carries the barrier and the max-over-ranks of 
               An `hbm` sub-object shows how far the path is from the HBM roofline.
     cpu_baseline  the reference's own softSsvThreshold256 (oracle/_ref, compiled from
               /root/reference) or, where that is absent, the C restatement (oracle/), on the
-              host cores, on a bounded slice of the same workload.
+              host cores, on a bounded slice of the same workload (250 k symbols per host thread x the
+              first 8000 rows: the ratio to it moves with the host's core count, so the per-core rate
+              is printed next to it). The same leg then replays sampled and tile-edge diagonals of
+              rank 0's hit list on that CPU code (`parity_check`): the line certifies its own hits.
+    strong    a second timed leg on ONE fixed database whatever N is: 320 Mbp x configs[2]'s table
+              (3,000 log-normal models, P_total ~ 1.19 M rows), cut into N shards with a 1.19 M-symbol
+              halo each -- the "sequence database sharded across the GPUs" of north_star, where
+              `value` above is N replicas of configs[1]. Hit count must be the same at every N.
+    e2e at N > 1 ends with ONE hit list on rank 0: every rank's device-sorted list is read back and
+              sent to rank 0 (gloo, host memory), where laying them end to end in rank order is the
+              global emission order.
 
 `--impl reference` times that CPU implementation alone, on all host threads, same metric.
 """
@@ -62,22 +72,11 @@ def log(*a):
 # ------------------------------------------------------------------------------------------
 # workload
 # ------------------------------------------------------------------------------------------
-def build_workload(n_gpus: int):
-    """Packed N x 100 Mbp sequence and the int8 score table of 100 models."""
-    lengths = synth.model_lengths(SEED, N_MODELS, LEN_LO, LEN_HI)
-    tables, conses = [], []
-    for i, L in enumerate(lengths):
-        t, c = synth.consensus_score_table(1000 + i, int(L))
-        tables.append(t)
-        conses.append(c)
-    table = np.concatenate(tables, axis=0)
-    n = SEQ_PER_GPU * n_gpus
-    packed = synth.random_packed(SEED, n)
-    # one mutated copy of every model's consensus per 10 Mbp so the hit list is not empty
-    g = synth.rng(SEED, 9)
-    for c in conses:
-        for _ in range(max(1, n // 10_000_000)):
-            frag = c.copy()
+def _plant(packed, n, models, copies_each, g):
+    """Overwrite windows of the packed sequence with 15 %-mutated copies of every model's consensus."""
+    for m in models:
+        for _ in range(copies_each):
+            frag = m.consensus.copy()
             mut = g.random(len(frag)) < 0.15
             frag[mut] = g.integers(0, 4, size=int(mut.sum()))
             at = int(g.integers(0, n - len(frag) - 8)) & ~3
@@ -85,7 +84,59 @@ def build_workload(n_gpus: int):
             window = synth.unpack_2bit(packed[at // 4: at // 4 + nb])
             window[: len(frag)] = frag
             packed[at // 4: at // 4 + nb] = synth.pack_2bit(window, pad_to_segment=False)
+
+
+def workload_hmm_path(tag="c2"):
+    return os.path.join(os.environ.get("TMPDIR", "/tmp"), f"havac_bench_{tag}_{os.getuid()}_{os.getpid()}.hmm")
+
+
+def build_table(lengths, model_seed, tag):
+    """Random HMMER3 models -> .hmm file -> the reference's threshold-256 projection at p = 0.02 (host C++,
+    bit-identical to PhmmReprojection.cpp:109-145, checked in tests/test_host_contracts.py). This is the
+    path a user's table takes; the bench does not time it."""
+    from havac_b200 import havac
+
+    models = synth.random_models(model_seed, lengths)
+    path = workload_hmm_path(tag)
+    synth.write_hmm(path, models)
+    try:
+        table, lens = havac.project_phmm(path, 0.02)
+    finally:
+        if not os.environ.get("HAVAC_BENCH_KEEP_HMM"):
+            os.unlink(path)
+    assert lens.tolist() == [int(x) for x in lengths]
+    return np.ascontiguousarray(table), models
+
+
+def build_workload(n_gpus: int):
+    """Packed N x 100 Mbp sequence and the int8 score table of 100 projected models (configs[1])."""
+    lengths = synth.model_lengths(SEED, N_MODELS, LEN_LO, LEN_HI)
+    table, models = build_table(lengths, 1000 + SEED, "c2")
+    n = SEQ_PER_GPU * n_gpus
+    packed = synth.random_packed(SEED, n)
+    # one mutated copy of every model's consensus per 10 Mbp so the hit list is not empty
+    _plant(packed, n, models, max(1, n // 10_000_000), synth.rng(SEED, 9))
     return packed, table, n, [int(x) for x in lengths]
+
+
+STRONG_SYMBOLS = 320_000_000
+STRONG_MODELS = 3000
+
+
+def lognormal_lengths(seed, count, mean, lo, hi):
+    g = synth.rng(seed, 21)
+    sigma = 0.6
+    x = g.lognormal(np.log(mean) - sigma * sigma / 2, sigma, size=count)
+    return np.clip(np.round(x), lo, hi).astype(np.int64)
+
+
+def build_strong_workload():
+    """The fixed database of the strong-scaling leg: 320 Mbp x configs[2]'s table shape."""
+    lengths = lognormal_lengths(3, STRONG_MODELS, 400, 50, 3000)
+    table, models = build_table(lengths, 3000, "c3")
+    packed = synth.random_packed(31, STRONG_SYMBOLS)
+    _plant(packed, STRONG_SYMBOLS, models, 1, synth.rng(31, 9))
+    return packed, table, STRONG_SYMBOLS
 
 
 def cpu_ssv_rate(packed, table, n_symbols, rows, threads, budget_cells):
@@ -162,15 +213,24 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------
 # arms
 # ------------------------------------------------------------------------------------------
+CPU_SYMBOLS_PER_THREAD = 250_000  # the CPU sample is fixed per host thread, so a step costs ~8 s whatever the core count
+CPU_ROWS = 8000
+
+
+def cpu_sample(threads, rows_total):
+    n_s, rows_s = CPU_SYMBOLS_PER_THREAD * threads, min(CPU_ROWS, rows_total)
+    text = (f"symbols [0,{n_s}) x rows [0,{rows_s}) of the workload per step ({CPU_SYMBOLS_PER_THREAD} symbols per host thread), "
+            f"split over {threads} threads with a rows-1 halo")
+    return n_s, rows_s, text
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
     packed, table, n, lengths = build_workload(max(1, args.gpus))  # the arm's own workload at this N
     rows_total = table.shape[0]
-    # bounded sample: 250 k symbols per host thread (4 Mbp on 16 threads) x the first 8000 rows of the same
-    # table per step, ~8 s a step whatever the core count, so the default 13 steps end within two minutes
-    n_s, rows_s = 250_000 * threads, min(8000, rows_total)
+    n_s, rows_s, sample = cpu_sample(threads, rows_total)
     vals = []
     for i in range(args.warmup + args.steps):
         g, kind, dt, nh = cpu_ssv_rate(packed, table, n_s, rows_s, threads, 0)
@@ -179,13 +239,13 @@ def run_reference(args, rank):
             vals.append((g, dt))
     value = float(np.mean([v for v, _ in vals]))
     ms = float(np.mean([d for _, d in vals]) * 1e3)
-    sample = f"symbols [0,{n_s}) x rows [0,{rows_s}) of the workload per step, split over {threads} threads with a rows-1 halo"
     out = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": value / PUBLISHED_FPGA_GCUPS, "dtype": "u8", "data": "synthetic",
         "config": {"workload": workload_name(max(1, args.gpus), rows_total), "sample": sample},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample,
+                         "per_core_value": value / threads},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -194,21 +254,49 @@ def run_reference(args, rank):
 
 def traffic_from_profile(symbols, rows):
     """dram__bytes_read.sum + dram__bytes_write.sum of one ssv_f16x2_kernel launch, from the committed
-    `ncu --set full` capture of this workload (profiles/r1_ncu_traffic.json); None when the capture
-    is of another shape."""
-    try:
-        with open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")) as fh:
-            t = json.load(fh)
-        if t.get("symbols") == symbols and t.get("rows") == rows:
-            return {"bytes_per_launch": t["dram_bytes_read"] + t["dram_bytes_write"], "source": t.get("source")}
-    except (OSError, ValueError, KeyError):
-        pass
+    `ncu --set full` capture of this workload (profiles/r2_ncu_traffic.json, else round 1's); None when the
+    capture is of another shape."""
+    for name in ("r2_ncu_traffic.json", "r1_ncu_traffic.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as fh:
+                t = json.load(fh)
+            if t.get("symbols") == symbols and t.get("rows") == rows:
+                return {"bytes_per_launch": t["dram_bytes_read"] + t["dram_bytes_write"], "source": t.get("source")}
+        except (OSError, ValueError, KeyError):
+            pass
     return None
 
 
 def workload_name(n_gpus, rows):
-    return (f"C2: {n_gpus} x 100 Mbp synthetic DNA x {N_MODELS} random models of {LEN_LO}-{LEN_HI} positions "
-            f"(P_total={rows}), threshold 256 (p=0.02 projection)")
+    return (f"C2: {n_gpus} x 100 Mbp synthetic DNA x {N_MODELS} random HMMER3 models of {LEN_LO}-{LEN_HI} positions "
+            f"(P_total={rows}), written to a .hmm file and projected to threshold 256 at p=0.02 by the host driver")
+
+
+def parity_self_check(packed, table, hits, geom, col_hi):
+    """Rank 0's hit list against the CPU code (outside every timed region): hit-carrying, uniformly sampled and
+    tile/thread-edge diagonals that lie wholly inside rank 0's columns must replay to exactly the GPU's rows."""
+    import oracle_lib as O
+
+    rows = table.shape[0]
+    t0 = time.perf_counter()
+    cell, seg, row = hits & np.uint64(0x3FFF), (hits >> np.uint64(14)) & np.uint64(0x3FFFFFF), (hits >> np.uint64(40)).astype(np.int64)
+    diag = (seg * np.uint64(12288) + cell).astype(np.int64) - row
+    inside = (diag >= 0) & (diag + rows <= col_hi)
+    ds, rs = diag[inside], row[inside]
+    order = np.argsort(ds, kind="stable")
+    ds, rs = ds[order], rs[order]
+    g = np.random.Generator(np.random.PCG64(7))
+    picks = ds[g.integers(0, len(ds), size=60)].tolist() if len(ds) else []
+    picks += g.integers(0, max(1, col_hi - rows), size=40).tolist()
+    picks += [d for d in O.edge_diagonals(geom, rows, col_hi, 3, 11) if d >= 0 and d + rows <= col_hi]
+    buf = np.zeros(1 << 16, dtype=np.uint32)
+    bad = 0
+    for d in picks:
+        a, b = np.searchsorted(ds, [d, d + 1])
+        if O.replay_diagonal(packed, table, int(d), buf) != set(rs[a:b].tolist()):
+            bad += 1
+    return {"diagonals_replayed": len(picks), "mismatches": bad, "seconds": round(time.perf_counter() - t0, 2),
+            "checker": "oracle/soft_ssv.c replay_diagonal (test/hmmerSsvRef/hmmerSsvRef.cpp:504-586 walk)"}
 
 
 def run_gpu(args, rank, world, local_rank):
@@ -220,6 +308,7 @@ def run_gpu(args, rank, world, local_rank):
         raise SystemExit("bench.py: no CUDA device; the SSV path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dist = None
+    gloo = None
     stdout_fd = None
     if world > 1:
         # NCCL writes its version banner to file descriptor 1; stdout must carry the one JSON line
@@ -229,25 +318,39 @@ def run_gpu(args, rank, world, local_rank):
         os.dup2(2, 1)
         import torch.distributed as dist  # noqa: F811
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        gloo = dist.new_group(backend="gloo")  # host-memory traffic: the hit lists gathered on rank 0
 
     def barrier():
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def reduce_max(x):
+    def reduce(x, op):
         if dist is None:
             return x
         t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=getattr(dist.ReduceOp, op))
         return float(t.item())
 
-    def reduce_sum(x):
+    def gather_hits(h):
+        """Every rank's (device-sorted) hit list to rank 0 through host memory; ranks hold increasing segment
+        ranges, so rank order is emission order. Returns (list on rank 0 or None, bytes moved to rank 0)."""
         if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+            return h, 0
+        counts = [None] * world
+        dist.all_gather_object(counts, int(len(h)), group=gloo)
+        if rank != 0:
+            if len(h):
+                dist.send(torch.from_numpy(h.view(np.int64)), dst=0, group=gloo)
+            return None, 0
+        out = np.empty(sum(counts), dtype=np.uint64)
+        out[: counts[0]] = h
+        at = counts[0]
+        for r in range(1, world):
+            if counts[r]:
+                dist.recv(torch.from_numpy(out[at: at + counts[r]].view(np.int64)), src=r, group=gloo)
+            at += counts[r]
+        return out, 8 * (len(out) - counts[0])
 
     t_setup = time.perf_counter()
     packed, table, n_total, lengths = build_workload(world)
@@ -261,7 +364,9 @@ def run_gpu(args, rank, world, local_rank):
     # host buffers of the e2e leg live in pinned memory (the copies are counted by the client)
     packed = torch.from_numpy(packed).pin_memory().numpy()
     table = torch.from_numpy(table).pin_memory().numpy()
+    t_open = time.perf_counter()
     client = HavacHwClient("", deviceIndex=local_rank)
+    device_open_s = reduce(time.perf_counter() - t_open, "MAX")
     if world > 1:
         client.setSegmentRange(seg_lo, seg_hi)
     client.writeSequence(packed)
@@ -288,14 +393,16 @@ def run_gpu(args, rank, world, local_rank):
     t_end = time.perf_counter()
     clocks = sampler.stop(t_begin, t_end)
     n_hits = client.getNumHits()
+    geom = client.tileGeometry()
     _, launches_per_step = client.runStats()
-    ms_dev = reduce_max(float(np.mean(ms_list)))
-    cells_all = reduce_sum(float(my_symbols) * rows)
-    hits_all = reduce_sum(float(n_hits))
+    ms_dev = reduce(float(np.mean(ms_list)), "MAX")
+    cells_all = reduce(float(my_symbols) * rows, "SUM")
+    hits_all = reduce(float(n_hits), "SUM")
     value = cells_all / (ms_dev * 1e-3) / 1e9
 
-    # ---- end to end through the client calls with host buffers ----------------------------
+    # ---- end to end through the client calls with host buffers, ONE hit list on rank 0 -----
     phases = {}
+    gathered = {"bytes": 0, "hits": 0}
 
     def e2e_step():
         t = [time.perf_counter()]
@@ -306,23 +413,65 @@ def run_gpu(args, rank, world, local_rank):
             raise RuntimeError("e2e run did not complete")
         t.append(time.perf_counter())
         h = client.getHitList(); t.append(time.perf_counter())
-        for name, a, b in zip(("writeSequence", "writePhmm", "run", "getHitList"), t, t[1:]):
+        whole, moved = gather_hits(h); t.append(time.perf_counter())
+        for name, a, b in zip(("writeSequence", "writePhmm", "run", "getHitList", "gatherOnRank0"), t, t[1:]):
             phases[name] = round((b - a) * 1e3, 3)
-        return h
+        gathered["bytes"] += moved
+        if whole is not None:
+            gathered["hits"] = int(len(whole))
+        return h, whole
 
     e2e_step()
+    gathered["bytes"] = 0
     h2d0, d2h0 = client.transferStats()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        hits = e2e_step()
+        hits, whole = e2e_step()
     barrier()
-    e2e_s = reduce_max((time.perf_counter() - t0) / args.steps)
+    e2e_s = reduce((time.perf_counter() - t0) / args.steps, "MAX")
     h2d1, d2h1 = client.transferStats()
     log(f"[rank {rank}] e2e phases of the last step (ms): {phases}")
     e2e_val = cells_all / e2e_s / 1e9
-    h2d = reduce_sum(float(h2d1 - h2d0)) / args.steps
-    d2h = reduce_sum(float(d2h1 - d2h0)) / args.steps
+    h2d = reduce(float(h2d1 - h2d0), "SUM") / args.steps
+    d2h = reduce(float(d2h1 - d2h0), "SUM") / args.steps
+    if rank == 0 and whole is not None and len(whole) > 1:  # the gathered list is in emission order as it stands
+        key = sharding.emission_order_key(whole).astype(np.int64)
+        if not np.all(np.diff(key) > 0):
+            raise RuntimeError("gathered hit list is not in emission order")
+
+    # ---- strong scaling: ONE fixed database cut into `world` shards ---------------------------
+    strong = None
+    if not args.no_strong:
+        s_packed, s_table, s_n = build_strong_workload()
+        s_rows = s_table.shape[0]
+        s_seg = len(s_packed) * 4 // synth.SEGMENT_SYMBOLS
+        s_lo, s_hi = sharding.plan_shards(s_seg, world)[rank]
+        s_mine = min(s_n, s_hi * synth.SEGMENT_SYMBOLS) - s_lo * synth.SEGMENT_SYMBOLS
+        if world > 1:
+            client.setSegmentRange(s_lo, s_hi)
+        client.writeSequence(s_packed)
+        client.writePhmm(s_table)
+        device_step()  # one warm-up pass of this shape; the clocks are up from the leg above
+        barrier()
+        s_ms = [device_step() for _ in range(args.strong_steps)]
+        barrier()
+        s_ms_dev = reduce(float(np.mean(s_ms)), "MAX")
+        s_hits = reduce(float(client.getNumHits()), "SUM")
+        t0 = time.perf_counter()
+        s_list, _ = gather_hits(client.getHitList())
+        s_gather = reduce(time.perf_counter() - t0, "MAX")
+        s_value = float(s_n) * s_rows / (s_ms_dev * 1e-3) / 1e9
+        strong = {"value": s_value, "unit": UNIT, "ms_per_step": s_ms_dev, "steps": args.strong_steps, "warmup": 1,
+                  "workload": f"{s_n // 1_000_000} Mbp x {STRONG_MODELS} log-normal models (P_total={s_rows}), p=0.02 projection, "
+                              f"ONE database cut into {world} shard(s)",
+                  "symbols": s_n, "rows": s_rows, "halo_symbols": s_rows - 1 if world > 1 else 0,
+                  "hits": int(s_hits), "hits_on_rank0_after_gather": (int(len(s_list)) if s_list is not None else None),
+                  "read_and_gather_hits_s": s_gather,
+                  "efficiency_vs_n1_hint": s_value / (world * (float(my_symbols) * rows / (ms_dev * 1e-3) / 1e9)),
+                  "efficiency_hint_basis": "strong GCUPS / (N x this run's per-GPU rate on the weak leg)",
+                  "shard_overhead_model": 1.0 / (1.0 + (s_rows * world / (2.0 * s_n) if world > 1 else 0.0))}
+        del s_packed, s_list
     client.close()
 
     if rank == 0:
@@ -351,27 +500,38 @@ def run_gpu(args, rank, world, local_rank):
                     "algorithmic_bytes_per_launch": hbm_bytes},
         }
         cores = os.cpu_count() or 1
-        n_s, rows_s = 4_000_000, min(8000, rows)  # ~10 s of host work on 16-24 cores
+        n_s, rows_s, sample = cpu_sample(cores, rows)
         g, kind, dt, nh = cpu_ssv_rate(packed, table, n_s, rows_s, cores, 0)
-        g1, _, dt1, _ = cpu_ssv_rate(packed, table, 250_000, rows_s, 1, 0)
-        cpu = {"value": g, "unit": UNIT, "cores": cores, "kind": kind, "seconds": dt,
+        g1, _, dt1, _ = cpu_ssv_rate(packed, table, CPU_SYMBOLS_PER_THREAD, rows_s, 1, 0)
+        cpu = {"value": g, "unit": UNIT, "cores": cores, "kind": kind, "seconds": dt, "per_core_value": g / cores,
                "single_thread_value": g1,
-               "sample": f"symbols [0,{n_s}) x rows [0,{rows_s}) of the workload, {cores} threads, rows-1 halo per chunk; "
-                         f"single thread on [0,250000) x the same rows"}
+               "sample": sample + f"; single thread on [0,{CPU_SYMBOLS_PER_THREAD}) x the same rows",
+               "parity_check": parity_self_check(packed, table, hits, geom, seg_hi * synth.SEGMENT_SYMBOLS)}
+        if cpu["parity_check"]["mismatches"]:
+            raise RuntimeError(f"bench hits disagree with the CPU replay: {cpu['parity_check']}")
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak",
-            # the reference publishes 1,739 GCUPS for this metric (one Alveo U50)
-            "vs_baseline": value / PUBLISHED_FPGA_GCUPS, "dtype": "u8 scores held as f16x2 (exact)", "data": "synthetic",
+            # the reference publishes 1,739 GCUPS for this metric (ONE Alveo U50), so the
+            # contract's value / published is the whole job against one card; the per-GPU figure is next to it
+            "vs_baseline": value / PUBLISHED_FPGA_GCUPS, "vs_baseline_per_gpu": value / world / PUBLISHED_FPGA_GCUPS,
+            "vs_baseline_note": f"{world} GPU(s) against the published figure of ONE Alveo U50 card",
+            "dtype": "u8 scores held as f16x2 (exact)", "data": "synthetic",
             "config": {"workload": workload_name(world, rows), "l2": "256 MiB written between steps (L2 flush)",
                        "symbols_per_gpu": SEQ_PER_GPU, "rows": rows, "hits": int(hits_all),
                        "parallelism": f"sequence axis sharded over {world} GPU(s), halo rows-1, no collective"},
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "ms_per_step": e2e_s * 1e3, "phases_ms": phases},
+                    "ms_per_step": e2e_s * 1e3, "phases_ms": phases,
+                    "hits_on_rank0_after_gather": gathered["hits"],
+                    "host_gather_bytes_per_step": int(gathered["bytes"] / args.steps),
+                    "ends_with": "one hit list in emission order in rank 0's host memory"},
+            "device_open_s": device_open_s,
             "gpu_launches": int(launches_per_step * args.steps * world),
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "published_fpga_gcups": PUBLISHED_FPGA_GCUPS,
         }
+        if strong is not None:
+            out["strong"] = strong
         if stdout_fd is not None:
             sys.stdout.flush()
             os.dup2(stdout_fd, 1)
@@ -389,6 +549,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="graft", choices=["graft", "reference"])
+    ap.add_argument("--strong-steps", type=int, default=2, help="timed passes of the strong-scaling leg")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     rank = int(os.environ.get("RANK", "0"))
@@ -402,7 +564,8 @@ def main():
         port = 29500 + os.getpid() % 2000
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.abspath(__file__),
-               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup)]
+               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup),
+               "--strong-steps", str(args.strong_steps)] + (["--no-strong"] if args.no_strong else [])
         raise SystemExit(subprocess.call(cmd))
     run_gpu(args, rank, world, local_rank)
 

@@ -30,7 +30,7 @@ EXPORTS = [
     "havac_cuda_abort", "havac_cuda_num_hits", "havac_cuda_read_hits", "havac_cuda_last_error",
     "havac_cuda_device_time_ms", "havac_cuda_device_count", "havac_cuda_run_stats", "havac_cuda_set_kernel", "havac_cuda_transfer_stats", "havac_cuda_sm_cycles",
     "havac_cuda_ingest_fasta", "havac_cuda_ingest_records", "havac_cuda_read_sequence", "havac_cuda_resolve_hits", "havac_cuda_project_phmm", "havac_cuda_read_phmm",
-    "havac_cuda_reverse_complement", "havac_cuda_strand_state",
+    "havac_cuda_reverse_complement", "havac_cuda_strand_state", "havac_cuda_tile_geometry", "havac_cuda_cell_selftest",
 ]
 
 
@@ -80,6 +80,9 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     L.havac_cuda_set_kernel.argtypes = [vp, C.c_char_p]
     L.havac_cuda_sm_cycles.argtypes = [vp, C.POINTER(u64)]
     L.havac_cuda_transfer_stats.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
+    L.havac_cuda_cell_selftest.argtypes = [vp, vp, vp]
+    L.havac_cuda_tile_geometry.argtypes = [vp, u32, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(u32), C.POINTER(u32),
+                                           C.POINTER(u32), C.POINTER(u32)]
     for name in EXPORTS:
         if name != "havac_cuda_last_error":
             getattr(L, name).restype = C.c_int
@@ -220,6 +223,22 @@ class HavacHwClient:
         a, b = C.c_uint64(0), C.c_uint64(0)
         self._ck(self._L.havac_cuda_transfer_stats(self._h, C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def cellSelftest(self):
+        """(score[2][65536], hit[2][65536]) of the fast kernel's cell update on every (prev, emission) pair."""
+        score = np.zeros(2 * 65536, dtype=np.uint8)
+        hit = np.zeros(2 * 65536, dtype=np.uint8)
+        self._ck(self._L.havac_cuda_cell_selftest(self._h, score.ctypes.data, hit.ctypes.data))
+        return score.reshape(2, 65536), hit.reshape(2, 65536)
+
+    def tileGeometry(self, device: int = 0) -> dict:
+        """How the last launch cut its work (havac_cuda_tile_geometry): for parity tests that aim at edges."""
+        lb, db = C.c_int64(0), C.c_int64(0)
+        nt, td, rc, br = C.c_uint32(0), C.c_uint32(0), C.c_uint32(0), C.c_uint32(0)
+        self._ck(self._L.havac_cuda_tile_geometry(self._h, device, C.byref(lb), C.byref(db), C.byref(nt), C.byref(td), C.byref(rc),
+                                                  C.byref(br)))
+        return {"loadBegin": lb.value, "diagBegin": db.value, "nTiles": nt.value, "tileDiagonals": td.value,
+                "rowChunk": rc.value, "blockRows": br.value}
 
     def close(self) -> None:
         if getattr(self, "_h", None) and self._h.value:

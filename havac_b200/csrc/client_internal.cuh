@@ -15,11 +15,22 @@ constexpr long long HALO_RESIDENT = 1ll << 24;       // symbols kept left of a s
 
 enum KernelKind { KERNEL_AUTO = 0, KERNEL_F16X2 = 1, KERNEL_SCALAR = 2 };
 
+struct DeviceResultBlock {
+  unsigned long long hitCount;  // total hits found (may exceed the capacity -> overflow)
+  unsigned long long cycles;    // SM cycles of CTA 0 (effective-clock probe)
+  int status;                   // SSV_STATUS_* bits
+  unsigned int tileCounter;     // next tile to hand out
+  int abort;                    // non-zero = stop; written from the control stream
+  int pad;
+};
+constexpr size_t RESULT_BYTES = 24;  // hitCount, cycles, status, tileCounter: what the host reads back
+
 struct DeviceCtx {
   int dev = 0;
   int numSMs = 0;
   cudaStream_t stream = nullptr;
   cudaEvent_t evStart = nullptr, evStop = nullptr;
+  cudaEvent_t evDone = nullptr;  // after the result block of the run has landed in hostRes
   // sequence shard
   uint32_t* dSeq = nullptr;
   size_t seqCap = 0;                   // bytes allocated at dSeq (kept across writes of the same size)
@@ -32,6 +43,10 @@ struct DeviceCtx {
   size_t tabCap = 0;  // bytes allocated at dTab8
   // outputs
   unsigned long long* dHits = nullptr;
+  // One 32-byte control block per device (DeviceResultBlock): cleared by ONE memset per launch, copied
+  // to pinned host memory by ONE asynchronous copy behind the stop event. The pointers below point into it.
+  DeviceResultBlock* dCtl = nullptr;
+  DeviceResultBlock* hostRes = nullptr;  // pinned
   unsigned long long* dHitCount = nullptr;
   unsigned int* dTileCounter = nullptr;
   int* dStatus = nullptr;
@@ -43,6 +58,9 @@ struct DeviceCtx {
   unsigned long long hitCount = 0;
   int status = 0;
   bool hitsSorted = false;  // dHits already put into emission order (hit_postprocess.cu)
+  // how the last launch cut its work (havac_cuda_tile_geometry)
+  long long lastLoadBegin = 0, lastDiagBegin = 0;
+  uint32_t lastTiles = 0, lastTileDiags = 0;
 };
 
 struct havac_cuda_client {
@@ -56,6 +74,7 @@ struct havac_cuda_client {
   uint64_t mirrorSymbols = 0;               // N when the resident sequence is the reverse complement over N symbols (strand.cu)
   uint32_t nRows = 0;
   bool launched = false, finished = false, aborted = false;
+  bool abortRequested = false;  // havac_cuda_abort/destroy asked for a stop: no repeat after a hit-buffer overflow
   int finalState = HAVAC_CUDA_STATE_NEW;
   int* hostOne = nullptr;    // pinned source word for the asynchronous abort write
   int kernel = KERNEL_AUTO;

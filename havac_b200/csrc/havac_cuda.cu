@@ -91,11 +91,7 @@ int launch_all(havac_cuda_client* c) {
   for (DeviceCtx& d : c->devs) {
     CK(cudaSetDevice(d.dev));
     d.hitsSorted = false;
-    CK(cudaMemsetAsync(d.dHitCount, 0, sizeof(unsigned long long), d.stream));
-    CK(cudaMemsetAsync(d.dTileCounter, 0, sizeof(unsigned int), d.stream));
-    CK(cudaMemsetAsync(d.dStatus, 0, sizeof(int), d.stream));
-    CK(cudaMemsetAsync(d.dCycles, 0, sizeof(unsigned long long), d.stream));
-    CK(cudaMemsetAsync(d.dAbort, 0, sizeof(int), d.stream));
+    CK(cudaMemsetAsync(d.dCtl, 0, sizeof(DeviceResultBlock), d.stream));  // counters, status and the abort flag
     CK(cudaEventRecord(d.evStart, d.stream));
     if (d.colEnd > d.colBegin) {
       SsvParams p{};
@@ -121,12 +117,19 @@ int launch_all(havac_cuda_client* c) {
       p.abortFlag = d.dAbort;
       p.status = d.dStatus;
       p.smCycles = d.dCycles;
+      d.lastLoadBegin = loadBegin;
+      d.lastDiagBegin = p.diagBegin;
+      d.lastTiles = p.nTiles;
+      d.lastTileDiags = SSV_TILE_DIAGS;
       if (c->kernel == KERNEL_SCALAR) ssv_launch_scalar(p, d.stream);
       else ssv_launch_f16x2(p, d.numSMs, d.stream);
       CK(cudaGetLastError());
       c->launches++;
     }
     CK(cudaEventRecord(d.evStop, d.stream));
+    // the results follow the stop event to pinned memory; nobody blocks in a cudaMemcpy later
+    CK(cudaMemcpyAsync(d.hostRes, d.dCtl, RESULT_BYTES, cudaMemcpyDeviceToHost, d.stream));
+    CK(cudaEventRecord(d.evDone, d.stream));
   }
   return HAVAC_CUDA_OK;
 }
@@ -139,16 +142,22 @@ bool grow_hit_buffers(havac_cuda_client* c, unsigned long long needed) {
     size_t freeB = 0, totalB = 0;
     if (cudaMemGetInfo(&freeB, &totalB) != cudaSuccess) return false;
     // the sort of the hits needs a second buffer of the same size later on
-    if ((double)newCap * 8.0 * 2.2 > (double)freeB + (double)c->hitCap * 8.0) return false;
+    if ((double)newCap * 8.0 * 2.2 > (double)freeB) return false;
   }
-  for (DeviceCtx& d : c->devs) {
-    cudaSetDevice(d.dev);
-    cudaFree(d.dHits);
-    d.dHits = nullptr;
-    if (cudaMalloc(&d.dHits, newCap * sizeof(unsigned long long)) != cudaSuccess) return false;
+  // the larger buffers are allocated BEFORE the old ones are freed: a failure leaves every device as it was
+  std::vector<unsigned long long*> fresh(c->devs.size(), nullptr);
+  bool ok = true;
+  for (size_t i = 0; i < c->devs.size() && ok; i++) {
+    cudaSetDevice(c->devs[i].dev);
+    if (cudaMalloc(&fresh[i], newCap * sizeof(unsigned long long)) != cudaSuccess) { fresh[i] = nullptr; cudaGetLastError(); ok = false; }
   }
-  c->hitCap = newCap;
-  return true;
+  for (size_t i = 0; i < c->devs.size(); i++) {
+    cudaSetDevice(c->devs[i].dev);
+    if (ok) { cudaFree(c->devs[i].dHits); c->devs[i].dHits = fresh[i]; }
+    else if (fresh[i]) cudaFree(fresh[i]);
+  }
+  if (ok) c->hitCap = newCap;
+  return ok;
 }
 
 // Pull the per-device results after the stop events have fired; decides the final state. A hit
@@ -162,11 +171,11 @@ int collect(havac_cuda_client* c, bool mayBlock = true) {
     unsigned long long most = 0;
     for (DeviceCtx& d : c->devs) {
       CK(cudaSetDevice(d.dev));
-      CK(cudaEventSynchronize(d.evStop));
-      CK(cudaMemcpy(&d.hitCount, d.dHitCount, sizeof d.hitCount, cudaMemcpyDeviceToHost));
-      CK(cudaMemcpy(&d.status, d.dStatus, sizeof d.status, cudaMemcpyDeviceToHost));
-      CK(cudaMemcpy(&d.cycles, d.dCycles, sizeof d.cycles, cudaMemcpyDeviceToHost));
-      c->d2hBytes += sizeof d.hitCount + sizeof d.status;
+      CK(cudaEventSynchronize(d.evDone));
+      d.hitCount = d.hostRes->hitCount;
+      d.status = d.hostRes->status;
+      d.cycles = d.hostRes->cycles;
+      c->d2hBytes += RESULT_BYTES;
       float ms = 0.f;
       CK(cudaEventElapsedTime(&ms, d.evStart, d.evStop));
       worst = std::max(worst, ms);
@@ -175,8 +184,9 @@ int collect(havac_cuda_client* c, bool mayBlock = true) {
       most = std::max<unsigned long long>(most, d.hitCount);
     }
     c->lastMs += worst;  // a repeated search counts in full
+    // a stop that was asked for wins over the repeat: launch_all would clear the abort flag again
+    if (overflow && c->abortRequested) aborted = true;
     if (overflow && !aborted && c->hitCapGrows && c->regrowths < 2) {
-      const unsigned long long before = c->hitCap;
       if (grow_hit_buffers(c, most)) {
         c->regrowths++;
         int rc = launch_all(c);
@@ -184,8 +194,6 @@ int collect(havac_cuda_client* c, bool mayBlock = true) {
         if (!mayBlock) { c->finalState = HAVAC_CUDA_STATE_RUNNING; return HAVAC_CUDA_OK; }
         continue;
       }
-      for (DeviceCtx& d : c->devs)  // could not grow: make sure every device still has a buffer
-        if (!d.dHits) { cudaSetDevice(d.dev); cudaMalloc(&d.dHits, before * sizeof(unsigned long long)); c->hitCap = before; }
     }
     c->finished = true;
     c->aborted = aborted;
@@ -294,7 +302,7 @@ int havac_cuda_create(const char* deviceSpec, uint32_t deviceIndex, havac_cuda_c
     cudaDeviceProp prop;
     if (!ck(cudaSetDevice(d.dev), "cudaSetDevice") || !ck(cudaGetDeviceProperties(&prop, d.dev), "cudaGetDeviceProperties"))
       return bail(HAVAC_CUDA_E_RUNTIME);
-    if (prop.major < 10) {
+    if (prop.major != 10) {  // sm_100a SASS only: a later major would fail at the first launch with 'no kernel image'
       c->err = "device " + std::to_string(d.dev) + " (" + prop.name + ") is sm_" + std::to_string(prop.major) +
                std::to_string(prop.minor) + "; this library carries sm_100a code only";
       return bail(HAVAC_CUDA_E_NODEVICE);
@@ -302,15 +310,19 @@ int havac_cuda_create(const char* deviceSpec, uint32_t deviceIndex, havac_cuda_c
     d.numSMs = prop.multiProcessorCount;
     if (!ck(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
         !ck(cudaStreamCreateWithFlags(&d.ctlStream, cudaStreamNonBlocking), "cudaStreamCreate") ||
-        !ck(cudaEventCreate(&d.evStart), "cudaEventCreate") || !ck(cudaEventCreate(&d.evStop), "cudaEventCreate"))
+        !ck(cudaEventCreate(&d.evStart), "cudaEventCreate") || !ck(cudaEventCreate(&d.evStop), "cudaEventCreate") ||
+        !ck(cudaEventCreateWithFlags(&d.evDone, cudaEventDisableTiming), "cudaEventCreate"))
       return bail(HAVAC_CUDA_E_RUNTIME);
     // the hit buffers are allocated once, like HavacHwClient::allocateOutputBuffers (HavacHwClient.cpp:73-76)
     if (!ck(cudaMalloc(&d.dHits, c->hitCap * sizeof(unsigned long long)), "cudaMalloc(hits)") ||
-        !ck(cudaMalloc(&d.dHitCount, sizeof(unsigned long long)), "cudaMalloc") ||
-        !ck(cudaMalloc(&d.dTileCounter, sizeof(unsigned int)), "cudaMalloc") ||
-        !ck(cudaMalloc(&d.dStatus, sizeof(int)), "cudaMalloc") ||
-        !ck(cudaMalloc(&d.dCycles, sizeof(unsigned long long)), "cudaMalloc") || !ck(cudaMalloc(&d.dAbort, sizeof(int)), "cudaMalloc"))
+        !ck(cudaMalloc(&d.dCtl, sizeof(DeviceResultBlock)), "cudaMalloc") ||
+        !ck(cudaHostAlloc((void**)&d.hostRes, sizeof(DeviceResultBlock), cudaHostAllocPortable), "cudaHostAlloc"))
       return bail(HAVAC_CUDA_E_NOMEM);
+    d.dHitCount = &d.dCtl->hitCount;
+    d.dCycles = &d.dCtl->cycles;
+    d.dStatus = &d.dCtl->status;
+    d.dTileCounter = &d.dCtl->tileCounter;
+    d.dAbort = &d.dCtl->abort;
   }
   *out = c;
   return HAVAC_CUDA_OK;
@@ -321,16 +333,14 @@ int havac_cuda_destroy(havac_cuda_client* c) {
   for (DeviceCtx& d : c->devs) {
     cudaSetDevice(d.dev);
     if (c->launched && !c->finished && d.dAbort && d.ctlStream)  // let a still-running kernel drain quickly
-      cudaMemcpyAsync(d.dAbort, c->hostOne, sizeof(int), cudaMemcpyHostToDevice, d.ctlStream);
+      c->abortRequested = true, cudaMemcpyAsync(d.dAbort, c->hostOne, sizeof(int), cudaMemcpyHostToDevice, d.ctlStream);
     if (d.stream) cudaStreamSynchronize(d.stream);
     free_sequence(d);
     free_table(d);
     if (d.dHits) cudaFree(d.dHits);
-    if (d.dHitCount) cudaFree(d.dHitCount);
-    if (d.dTileCounter) cudaFree(d.dTileCounter);
-    if (d.dStatus) cudaFree(d.dStatus);
-    if (d.dCycles) cudaFree(d.dCycles);
-    if (d.dAbort) cudaFree(d.dAbort);
+    if (d.dCtl) cudaFree(d.dCtl);
+    if (d.hostRes) cudaFreeHost(d.hostRes);
+    if (d.evDone) cudaEventDestroy(d.evDone);
     if (d.ctlStream) cudaStreamDestroy(d.ctlStream);
     if (d.evStart) cudaEventDestroy(d.evStart);
     if (d.evStop) cudaEventDestroy(d.evStop);
@@ -461,6 +471,7 @@ int havac_cuda_invoke_async(havac_cuda_client* c) {
   if (c->launched && !c->finished) return fail(c, HAVAC_CUDA_E_LOGIC, "a run is already in flight");
   c->regrowths = 0;
   c->lastMs = 0.f;
+  c->abortRequested = false;
   int rc = launch_all(c);
   if (rc) return rc;
   c->launched = true;
@@ -478,7 +489,7 @@ int havac_cuda_state(havac_cuda_client* c, int* state) {
   bool allDone = true, anyStarted = false;
   for (DeviceCtx& d : c->devs) {
     CK(cudaSetDevice(d.dev));
-    cudaError_t e = cudaEventQuery(d.evStop);
+    cudaError_t e = cudaEventQuery(d.evDone);
     if (e == cudaErrorNotReady) allDone = false;
     else if (e != cudaSuccess) { c->err = cudaGetErrorString(e); *state = HAVAC_CUDA_STATE_ERROR; return HAVAC_CUDA_E_RUNTIME; }
     if (cudaEventQuery(d.evStart) == cudaSuccess) anyStarted = true;
@@ -519,6 +530,7 @@ int havac_cuda_abort(havac_cuda_client* c, int* state) {
   if (!c) return HAVAC_CUDA_E_INVALID;
   if (!c->launched) return fail(c, HAVAC_CUDA_E_LOGIC, "nothing was launched");
   if (!c->finished) {
+    c->abortRequested = true;
     for (DeviceCtx& d : c->devs) {
       CK(cudaSetDevice(d.dev));
       // wait until the run has actually started, or the memset that opens it would clear the flag
@@ -607,6 +619,36 @@ int havac_cuda_transfer_stats(havac_cuda_client* c, uint64_t* h2d, uint64_t* d2h
   if (!c) return HAVAC_CUDA_E_INVALID;
   if (h2d) *h2d = c->h2dBytes;
   if (d2h) *d2h = c->d2hBytes;
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_cell_selftest(havac_cuda_client* c, uint8_t* score, uint8_t* hit) {
+  if (!c || !score || !hit) return HAVAC_CUDA_E_INVALID;
+  DeviceCtx& d = c->devs[0];
+  CK(cudaSetDevice(d.dev));
+  uint8_t* buf = nullptr;
+  CK(cudaMalloc(&buf, 4 * 65536));
+  ssv_launch_cell_selftest(buf, buf + 2 * 65536, d.stream);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpyAsync(score, buf, 2 * 65536, cudaMemcpyDeviceToHost, d.stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(hit, buf + 2 * 65536, 2 * 65536, cudaMemcpyDeviceToHost, d.stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(d.stream);
+  cudaFree(buf);
+  if (e != cudaSuccess) return fail(c, HAVAC_CUDA_E_RUNTIME, std::string("cell_selftest: ") + cudaGetErrorString(e));
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_tile_geometry(havac_cuda_client* c, uint32_t device, int64_t* loadBegin, int64_t* diagBegin, uint32_t* nTiles,
+                             uint32_t* tileDiagonals, uint32_t* rowChunk, uint32_t* blockRows) {
+  if (!c || device >= c->devs.size()) return HAVAC_CUDA_E_INVALID;
+  if (!c->launched) return fail(c, HAVAC_CUDA_E_LOGIC, "nothing was launched");
+  const DeviceCtx& d = c->devs[device];
+  if (loadBegin) *loadBegin = d.lastLoadBegin;
+  if (diagBegin) *diagBegin = d.lastDiagBegin;
+  if (nTiles) *nTiles = d.lastTiles;
+  if (tileDiagonals) *tileDiagonals = d.lastTileDiags;
+  if (rowChunk) *rowChunk = SSV_ROW_CHUNK;
+  if (blockRows) *blockRows = SSV_BLOCK_ROWS;
   return HAVAC_CUDA_OK;
 }
 

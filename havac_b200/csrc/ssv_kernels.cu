@@ -644,11 +644,40 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_tail_kernel(
   ssv_f16x2_body<true>(prm);
 }
 
+// Every (previous score, emission) pair through the fast path's own cell update, for the exhaustive parity
+// test against the FPGA cell (device/HavacHls.cpp:370-402): thread i takes pair i in the low fp16 half and pair
+// 65535 - i in the high half, so both halves and their independence are covered in one launch.
+__global__ void cell_selftest_kernel(uint8_t* __restrict__ outScore, uint8_t* __restrict__ outHit) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 65536u) return;
+  const uint32_t j = 65535u - i;
+  auto enc = [](int v) { return (uint32_t)__half_as_ushort(__int2half_rn(v * 256)); };
+  const uint32_t w = enc((int)(i >> 8)) | (enc((int)(j >> 8)) << 16);
+  const uint32_t m = enc((int)(i & 255u) - 128) | (enc((int)(j & 255u) - 128) << 16);
+  const uint32_t r = hfma2_relu_add(m, w);
+  const uint32_t lo = r & 0xffffu, hi = r >> 16;
+  const bool hitLo = lo == 0x7c00u, hitHi = hi == 0x7c00u;
+  // the kernel's own test sees an inf exactly where a half is 0x7c00
+  const bool seen = has_inf(r);
+  const int sLo = hitLo ? 0 : __half2int_rn(__ushort_as_half((unsigned short)lo)) / 256;
+  const int sHi = hitHi ? 0 : __half2int_rn(__ushort_as_half((unsigned short)hi)) / 256;
+  // low half reports pair i; the high half's result must equal what thread j's low half reports: written to
+  // a second plane so the host can compare the two
+  outScore[i] = (uint8_t)sLo;
+  outHit[i] = (uint8_t)((hitLo ? 1 : 0) | ((seen == (hitLo || hitHi)) ? 0 : 0x80));
+  outScore[65536u + j] = (uint8_t)sHi;
+  outHit[65536u + j] = (uint8_t)(hitHi ? 1 : 0);
+}
+
 }  // namespace
 
 // =======================================================================================
 // launchers
 // =======================================================================================
+void ssv_launch_cell_selftest(uint8_t* outScore, uint8_t* outHit, void* stream) {
+  cell_selftest_kernel<<<256, 256, 0, (cudaStream_t)stream>>>(outScore, outHit);
+}
+
 void ssv_launch_table_prep(const int8_t* tab8, uint32_t nRows, uint2* tab16, uint32_t rowsPadded,
                            void* stream) {
   table_prep_kernel<<<(rowsPadded + 255) / 256, 256, 0, (cudaStream_t)stream>>>(tab8, nRows, tab16,

@@ -59,3 +59,5 @@ void ssv_launch_project_table(const float* emissions, uint32_t nRows, const uint
 void ssv_launch_f16x2(const SsvParams& prm, int numSMs, void* stream);
 void ssv_launch_scalar(const SsvParams& prm, void* stream);
 int ssv_f16x2_ctas_per_sm();
+// 2 x 65536 bytes each: plane 0 = the low fp16 half's result for pair i = prev * 256 + (e + 128), plane 1 = the high half's
+void ssv_launch_cell_selftest(uint8_t* outScore, uint8_t* outHit, void* stream);

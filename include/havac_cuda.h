@@ -171,6 +171,17 @@ int havac_cuda_run_stats(havac_cuda_client* c, uint64_t* cells, uint32_t* launch
 int havac_cuda_sm_cycles(havac_cuda_client* c, uint64_t* cycles);
 /* Running totals of the bytes this client copied host->device and device->host. */
 int havac_cuda_transfer_stats(havac_cuda_client* c, uint64_t* h2dBytes, uint64_t* d2hBytes);
+/* The fast kernel's cell update on all 65,536 (previous score 0..255, emission -128..127) pairs, one launch:
+ * score[i] / hit[i] for pair i = prev * 256 + (emission + 128) computed in the low fp16 half, score[65536 + i] /
+ * hit[65536 + i] the same pair computed in the high half. hit bit 7 set = the kernel's own overflow test disagreed
+ * with the halves. Both buffers hold 131,072 bytes. Checked against device/HavacHls.cpp:370-402 in the tests. */
+int havac_cuda_cell_selftest(havac_cuda_client* c, uint8_t* score, uint8_t* hit);
+/* How the last launch on device `device` of this client cut its work: global column of the first resident
+ * symbol the kernel was given, first diagonal (column - row, relative to that symbol) of tile 0, number of
+ * tiles, diagonals per tile, rows per staged score-table chunk, rows per unrolled block. Parity tests use
+ * it to aim their diagonal replays at tile / thread / chunk / block edges. Any pointer may be NULL. */
+int havac_cuda_tile_geometry(havac_cuda_client* c, uint32_t device, int64_t* loadBegin, int64_t* diagBegin, uint32_t* nTiles,
+                             uint32_t* tileDiagonals, uint32_t* rowChunk, uint32_t* blockRows);
 /* Select a kernel variant by name ("auto" | "f16x2" | "scalar"); for tests that
  * cross-check the fast path against the plain one. */
 int havac_cuda_set_kernel(havac_cuda_client* c, const char* name);

@@ -181,10 +181,107 @@ def replay_diagonal(packed, table, d, buf=None):
     return set(buf[:k].tolist())
 
 
-def check_hits_by_replay(packed, table, raw_hits, n_hit_diagonals, n_random_diagonals, seed):
+DIAG_EDGE_OFFSETS = (0, 1, 2, 31, 32, 33, 62, 63, 64)  # thread edges (32 diagonals a thread), register halves
+
+
+def edge_diagonals(geom, rows, n_columns, n_tiles, seed):
+    """Global diagonals (column - row) that sit on the fast kernel's STRUCTURE edges rather than anywhere:
+    for the first tiles (the band left of column 0), the last tile and randomly drawn ones, the first and last
+    diagonals of the tile, of its threads and of their register halves, and the middle of the tile.
+    `geom` is HavacHwClient.tileGeometry() of the run being checked."""
+    W = geom["tileDiagonals"]
+    origin = geom["loadBegin"] + geom["diagBegin"]
+    g = np.random.Generator(np.random.PCG64(seed))
+    nt = geom["nTiles"]
+    tiles = {0, 1, nt - 1, nt - 2} | set(g.integers(0, nt, size=n_tiles).tolist())
+    offs = list(DIAG_EDGE_OFFSETS) + [W // 2 - 1, W // 2] + [W - 1 - o for o in DIAG_EDGE_OFFSETS]
+    out = []
+    for t in sorted(x for x in tiles if 0 <= x < nt):
+        for o in offs:
+            d = origin + t * W + o
+            if -(rows - 1) <= d < n_columns:
+                out.append(d)
+    return out
+
+
+def set_symbols(packed, col, syms):
+    """Overwrite symbols [col, col + len(syms)) of a 2-bit packed buffer."""
+    for k, x in enumerate(np.asarray(syms).tolist()):
+        c = col + k
+        sh = 2 * (c & 3)
+        packed[c >> 2] = (int(packed[c >> 2]) & ~(3 << sh) & 0xFF) | (int(x) << sh)
+
+
+def plant_hit_at(packed, table, d, r_star, g):
+    """Edit the packed sequence along diagonal d so that the score crosses 256 at EXACTLY row r_star: a run of
+    each row's worst symbol long enough to bring any score to 0, then each row's best symbol from a start row
+    chosen (with a few demotions to the second-best symbol where the sums skip) so that the running sum is
+    < 256 at r_star - 1 and >= 256 at r_star. Returns the first row edited, or None if no run fits."""
+    t = np.asarray(table, dtype=np.int64).reshape(-1, 4)
+    best, worst = t.argmax(axis=1), t.argmin(axis=1)
+    order = np.argsort(t, axis=1)
+    for attempt in range(200):
+        sym = best.copy()
+        if attempt:  # demote a few rows near the target to their second-best symbol: moves the crossing
+            for r in g.integers(max(0, r_star - 40), r_star + 1, size=1 + attempt % 4).tolist():
+                sym[r] = order[r, 2]
+        sc = t[np.arange(len(t)), sym]
+        for a in range(r_star, max(-1, r_star - 120), -1):
+            run = sc[a:r_star + 1]
+            c = np.cumsum(run)
+            if (c < 0).any():
+                break
+            if c[-1] >= 256:
+                if len(c) == 1 or c[:-1].max() < 256:
+                    # zeroing run in front of row a
+                    z, acc = a, 0
+                    while z > 0 and acc > -256:
+                        z -= 1
+                        acc += t[z, worst[z]]
+                    if acc > -256 or d + z < 0 or d + r_star >= len(packed) * 4:
+                        return None
+                    syms = np.concatenate([worst[z:a], sym[a:r_star + 1]]).astype(np.uint8)
+                    set_symbols(packed, d + z, syms)
+                    return z
+                break
+    return None
+
+
+def edge_targets(geom, rows, n_columns, seed, n_tiles=5):
+    """(diagonal, row) pairs for plant_hit_at: diagonals on tile / thread / register-half edges crossed with rows on
+    block edges (r = 0, -1 mod blockRows), row-chunk edges (r = 0, -1 mod rowChunk) and the table's last row."""
+    B, TC = geom["blockRows"], geom["rowChunk"]
+    g = np.random.Generator(np.random.PCG64(seed))
+    row_targets = [rows - 1]
+    for k in range(1, 6):
+        for base in (k * TC, (rows // TC) * TC if k == 1 else 0):
+            for r in (base - 1, base):
+                if 200 <= r < rows:
+                    row_targets.append(r)
+    for _ in range(8):
+        b = int(g.integers(8, max(9, rows // B))) * B
+        row_targets += [r for r in (b - 1, b) if 200 <= r < rows]
+    row_targets = sorted(set(row_targets))
+    diags = [d for d in edge_diagonals(geom, rows, n_columns, n_tiles, seed + 1) if d >= 0 and d + rows < n_columns]
+    out, used = [], []
+    k = int(g.integers(0, len(row_targets)))
+    for d in diags:
+        for _ in range(len(row_targets)):
+            r = row_targets[k % len(row_targets)]
+            k += 1
+            lo, hi = d + r - 400, d + r + 2  # columns a planting may touch
+            if all(hi < a or lo > b for a, b in used):
+                used.append((lo, hi))
+                out.append((d, r))
+                break
+    return out
+
+
+def check_hits_by_replay(packed, table, raw_hits, n_hit_diagonals, n_random_diagonals, seed, geom=None, n_edge_tiles=6):
     """Scalable verification: (1) sampled diagonals that carry GPU hits replay to
     exactly those hit rows, (2) uniformly sampled diagonals replay to exactly the GPU's hits on
-    them (usually none). Returns the number of diagonals checked."""
+    them (usually none), (3) with `geom` (HavacHwClient.tileGeometry()), the diagonals on the edges of
+    tiles, threads and register halves do too. Returns the number of diagonals checked."""
     raw = np.asarray(raw_hits, dtype=np.uint64)
     rows = np.asarray(table).reshape(-1, 4).shape[0]
     cell, seg, row = raw & np.uint64(0x3fff), (raw >> np.uint64(14)) & np.uint64(0x3ffffff), raw >> np.uint64(40)
@@ -206,4 +303,9 @@ def check_hits_by_replay(packed, table, raw_hits, n_hit_diagonals, n_random_diag
         got = replay_diagonal(packed, table, d, buf)
         assert got == by_diag.get(d, set()), f"sampled diagonal {d}"
         checked += 1
+    if geom is not None:
+        for d in edge_diagonals(geom, rows, len(packed) * 4, n_edge_tiles, seed + 17):
+            got = replay_diagonal(packed, table, d, buf)
+            assert got == by_diag.get(d, set()), f"edge diagonal {d} (tile offset {(d - geom['loadBegin'] - geom['diagBegin']) % geom['tileDiagonals']})"
+            checked += 1
     return checked

@@ -35,3 +35,32 @@ def test_reference_arm_line(monkeypatch, capsys):
     assert d["e2e"] == {"value": 3.5, "unit": bench.UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     # the sample is a slice of the workload: a bounded number of symbols per host thread, the first rows of the table
     assert seen["n"] == 250_000 * seen["threads"] and seen["rows"] == min(8000, seen["table_rows"])
+
+
+def test_bench_table_is_the_reference_projection(monkeypatch):
+    """bench.py's score table is what its label says: random HMMER3 models written to a .hmm file and projected
+    to threshold 256 at p = 0.02 -- byte for byte what the UNMODIFIED reference objects (P7HmmReader +
+    PhmmReprojection + PhmmPreprocessor, compiled into oracle/_ref) make of the same file."""
+    import numpy as np
+    import pytest
+
+    import bench
+    import oracle_lib as O
+    from havac_b200 import synth
+
+    if O.ref() is None:
+        pytest.skip("oracle/_ref not built (no /root/reference here)")
+    monkeypatch.setenv("HAVAC_BENCH_KEEP_HMM", "1")
+    lengths = synth.model_lengths(bench.SEED, bench.N_MODELS, bench.LEN_LO, bench.LEN_HI)
+    table, models = bench.build_table(lengths, 1000 + bench.SEED, "c2test")
+    path = bench.workload_hmm_path("c2test")
+    try:
+        want, lens = O.ref_load_phmm(path, 0.02)
+    finally:
+        os.unlink(path)
+    assert lens.tolist() == [int(x) for x in lengths]
+    assert np.array_equal(table.reshape(-1), want)
+    # and build_workload uses exactly this table
+    monkeypatch.delenv("HAVAC_BENCH_KEEP_HMM")
+    _, table2, n, _ = bench.build_workload(1)
+    assert n == bench.SEQ_PER_GPU and np.array_equal(table2, table)

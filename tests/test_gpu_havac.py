@@ -208,11 +208,16 @@ def test_two_clients_on_one_gpu_run_side_by_side():
 
 def test_full_size_properties_c2():
     """BASELINE configs[1] size (100 Mbp x ~35 k rows), where brute force on the CPU is impossible:
-    (1) every GPU hit replays to a hit at exactly that row on its diagonal (no false positives),
-    (2) a fixed sample of whole diagonals replayed on the CPU has exactly the GPU's hits (bounds
-    false negatives), (3) segment-range shards reproduce the whole run."""
+    (0) hits are PLANTED so that they fall on the fast kernel's structure edges -- diagonals first/last in a
+        tile, in a thread's 32 and in a register half, crossed with rows first/last in a 32-row block, in a
+        2048-row chunk and the table's last row -- and every one of them must be reported,
+    (1) the fast kernel's hit set == the plain kernel's on the WHOLE matrix (exact: the plain kernel is an
+        independently written integer kernel that is itself pinned to the oracle at small sizes),
+    (2) every sampled hit diagonal, uniformly sampled diagonal and edge diagonal replays on the CPU oracle to
+        exactly the GPU's hit rows, (3) segment-range shards reproduce the whole run."""
     import bench
     packed, table, n, _ = bench.build_workload(1)
+    packed = packed.copy()
     rows = table.shape[0]
     c = HavacHwClient("")
     try:
@@ -220,7 +225,29 @@ def test_full_size_properties_c2():
         c.writePhmm(table)
         c.invokeHavacSsvAsync()
         assert c.waitForHavacSsvAsync() == STATE_COMPLETED
+        geom = c.tileGeometry()
+        # (0) plant hits on the structure edges this launch geometry has, then search again
+        g = np.random.Generator(np.random.PCG64(2024))
+        planted = []
+        for d, r in O.edge_targets(geom, rows, n, seed=5):
+            if O.plant_hit_at(packed, table, d, r, g) is not None:
+                planted.append((d, r))
+        assert len(planted) >= 40, f"only {len(planted)} edge hits could be planted"
+        B, TC, W = geom["blockRows"], geom["rowChunk"], geom["tileDiagonals"]
+        origin = geom["loadBegin"] + geom["diagBegin"]
+        assert {r % B for _, r in planted} >= {0, B - 1} and {r % TC for _, r in planted} >= {0, TC - 1}
+        assert {(d - origin) % W for d, _ in planted} >= {0, 1, 31, 32, W - 2, W - 1}
+        c.writeSequence(packed)
+        c.invokeHavacSsvAsync()
+        assert c.waitForHavacSsvAsync() == STATE_COMPLETED
         whole = c.getHitList()
+        fast_ms = c.deviceTimeMs()
+        c.setKernel("scalar")
+        c.invokeHavacSsvAsync()
+        assert c.waitForHavacSsvAsync() == STATE_COMPLETED
+        plain = c.getHitList()
+        plain_ms = c.deviceTimeMs()
+        c.setKernel("f16x2")
         n_seg = len(packed) * 4 // 12288
         parts = []
         for lo, hi in sharding.plan_shards(n_seg, 3):
@@ -232,29 +259,12 @@ def test_full_size_properties_c2():
     finally:
         c.close()
     assert len(whole) > 1000
+    print(f"C2 full size: {len(whole)} hits, f16x2 {fast_ms:.1f} ms, scalar {plain_ms:.1f} ms, {len(planted)} edge hits planted")
+    assert np.array_equal(whole, plain), "fast kernel and plain kernel disagree on the full C2 matrix"
     assert np.array_equal(sharding.merge_hits(parts), whole)
-    cell, seg, row = whole & np.uint64(0x3fff), (whole >> np.uint64(14)) & np.uint64(0x3ffffff), whole >> np.uint64(40)
-    pos = (seg * np.uint64(12288) + cell).astype(np.int64)
-    row = row.astype(np.int64)
-    diag = pos - row
-    L = O.oracle()
-    flat = np.ascontiguousarray(table).reshape(-1)
-    g = synth.rng(74, 1)
-    buf = np.zeros(4096, dtype=np.uint32)
-    W = rows + 8  # a window of the sequence around one diagonal
-
-    def replay(d):
-        a = max(0, d)  # first column of the diagonal
-        b = min(len(packed) * 4, d + rows)
-        lo = (a // 4) * 4
-        sym = synth.unpack_2bit(packed[lo // 4:(b + 3) // 4])
-        k = L.oracle_replay_diagonal(sym, b - lo, flat, rows, d - lo, buf, len(buf))
-        return set(buf[:k].tolist())
-
-    by_diag = {}
-    for d, r in zip(diag.tolist(), row.tolist()):
-        by_diag.setdefault(d, set()).add(r)
-    for d in g.choice(np.array(sorted(by_diag)), size=min(400, len(by_diag)), replace=False).tolist():
-        assert replay(d) == by_diag[d], f"diagonal {d}"
-    for d in g.integers(-(rows - 1), n, size=300).tolist():
-        assert replay(d) == by_diag.get(d, set()), f"sampled diagonal {d}"
+    have = set(whole.tolist())
+    for d, r in planted:
+        assert int(O.encode_hits([d + r], [r])[0]) in have, f"planted edge hit (diagonal {d}, row {r}) was not reported"
+    checked = O.check_hits_by_replay(packed, table, whole, n_hit_diagonals=400, n_random_diagonals=300, seed=74, geom=geom,
+                                     n_edge_tiles=8)
+    assert checked > 700

@@ -179,3 +179,34 @@ def test_every_tail_length():
         assert (want >> np.uint64(40)).max() == rows - 1, "no hit in the last row: the case would prove nothing"
         got = np.sort(gpu_hits(packed, t, "f16x2"))
         assert np.array_equal(got, want), f"rows={rows}: {len(got)} hits vs oracle {len(want)}"
+
+
+def test_cell_update_exhaustive():
+    """All 65,536 (previous score, emission) pairs through the fast kernel's own cell update -- one
+    fma.rn.relu.f16x2 on 256 x score, an overflow to +inf standing for "hit" -- in the low and in the high fp16
+    half, against the FPGA cell of device/HavacHls.cpp:370-402 (oracle_cell_processor): same next score, same
+    hit flag, and the kernel's overflow test fires exactly where a half hit. This is what `dtype` in the bench
+    line means by "u8 scores held as f16x2 (exact)"."""
+    import ctypes as C
+    L = O.oracle()
+    want_score = np.zeros(65536, dtype=np.uint8)
+    want_hit = np.zeros(65536, dtype=np.uint8)
+    s, h = C.c_uint8(0), C.c_int(0)
+    for prev in range(256):
+        for e in range(-128, 128):
+            L.oracle_cell_processor(prev, e, C.byref(s), C.byref(h))
+            want_score[prev * 256 + e + 128] = s.value
+            want_hit[prev * 256 + e + 128] = h.value
+    # the recurrence of test/softSsv/SoftSsv.cpp:39-49 says the same thing
+    pe = np.arange(256)[:, None] + np.arange(-128, 128)[None, :]
+    assert np.array_equal(want_hit.reshape(256, 256), (pe >= 256).astype(np.uint8))
+    assert np.array_equal(want_score.reshape(256, 256), np.where((pe < 0) | (pe >= 256), 0, pe).astype(np.uint8))
+    c = HavacHwClient("")
+    try:
+        score, hit = c.cellSelftest()
+    finally:
+        c.close()
+    assert not (hit & 0x80).any(), "has_inf() disagrees with the halves"
+    for half in (0, 1):
+        assert np.array_equal(hit[half] & 1, want_hit), f"hit flags differ in fp16 half {half}"
+        assert np.array_equal(score[half], want_score), f"scores differ in fp16 half {half}"
