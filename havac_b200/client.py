@@ -31,7 +31,12 @@ EXPORTS = [
     "havac_cuda_device_time_ms", "havac_cuda_device_count", "havac_cuda_run_stats", "havac_cuda_set_kernel", "havac_cuda_transfer_stats", "havac_cuda_sm_cycles",
     "havac_cuda_ingest_fasta", "havac_cuda_ingest_records", "havac_cuda_read_sequence", "havac_cuda_resolve_hits", "havac_cuda_project_phmm", "havac_cuda_read_phmm",
     "havac_cuda_reverse_complement", "havac_cuda_strand_state", "havac_cuda_tile_geometry", "havac_cuda_cell_selftest",
+    "havac_cuda_trace_cells", "havac_cuda_debug_poke_phmm",
 ]
+
+# one cell of the per-cell trace (include/havac_cuda.h havac_cuda_cell_record; byCellComparator.hpp:23-31)
+CELL_RECORD = np.dtype([("prevValue", np.uint8), ("matchScore", np.int8), ("cellValue", np.uint8), ("phmmVector", np.int8, (4,)),
+                        ("symbol", np.uint8), ("passesThreshold", np.uint8), ("pad", np.uint8, (3,))])
 
 
 class LogicError(RuntimeError):
@@ -81,6 +86,8 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     L.havac_cuda_sm_cycles.argtypes = [vp, C.POINTER(u64)]
     L.havac_cuda_transfer_stats.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
     L.havac_cuda_cell_selftest.argtypes = [vp, vp, vp]
+    L.havac_cuda_trace_cells.argtypes = [vp, u32, u32, u64, u64, vp, u64, C.POINTER(u64)]
+    L.havac_cuda_debug_poke_phmm.argtypes = [vp, u64, C.c_int8]
     L.havac_cuda_tile_geometry.argtypes = [vp, u32, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(u32), C.POINTER(u32),
                                            C.POINTER(u32), C.POINTER(u32)]
     for name in EXPORTS:
@@ -223,6 +230,16 @@ class HavacHwClient:
         a, b = C.c_uint64(0), C.c_uint64(0)
         self._ck(self._L.havac_cuda_transfer_stats(self._h, C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def traceCells(self, rowBegin: int, rowEnd: int, colBegin: int, colEnd: int) -> np.ndarray:
+        """Per-cell records [rowEnd - rowBegin, colEnd - colBegin] of the window, computed on the device."""
+        out = np.zeros((rowEnd - rowBegin, colEnd - colBegin), dtype=CELL_RECORD)
+        n = C.c_uint64(0)
+        self._ck(self._L.havac_cuda_trace_cells(self._h, rowBegin, rowEnd, colBegin, colEnd, out.ctypes.data, out.size, C.byref(n)))
+        return out
+
+    def debugPokePhmm(self, byteOffset: int, value: int) -> None:
+        self._ck(self._L.havac_cuda_debug_poke_phmm(self._h, byteOffset, value))
 
     def cellSelftest(self):
         """(score[2][65536], hit[2][65536]) of the fast kernel's cell update on every (prev, emission) pair."""

@@ -622,6 +622,55 @@ int havac_cuda_transfer_stats(havac_cuda_client* c, uint64_t* h2d, uint64_t* d2h
   return HAVAC_CUDA_OK;
 }
 
+int havac_cuda_trace_cells(havac_cuda_client* c, uint32_t rowBegin, uint32_t rowEnd, uint64_t colBegin, uint64_t colEnd,
+                           havac_cuda_cell_record* out, uint64_t capRecords, uint64_t* nRecords) {
+  static_assert(sizeof(havac_cuda_cell_record) == sizeof(SsvCellRecord), "record layouts must agree");
+  if (!c) return HAVAC_CUDA_E_INVALID;
+  if (c->devs.size() != 1) return fail(c, HAVAC_CUDA_E_LOGIC, "the per-cell trace runs on a single-device client");
+  if (c->launched && !c->finished) return fail(c, HAVAC_CUDA_E_LOGIC, "a run is in flight");
+  DeviceCtx& d = c->devs[0];
+  if (!d.dSeq || !d.dTab8) return fail(c, HAVAC_CUDA_E_LOGIC, "write the sequence and the score table first");
+  if (rowEnd > c->nRows || rowBegin >= rowEnd || colBegin >= colEnd || (long long)colEnd > d.resEnd || (long long)colBegin < d.resBegin)
+    return fail(c, HAVAC_CUDA_E_LENGTH, "trace window outside the resident matrix");
+  const uint64_t n = (uint64_t)(rowEnd - rowBegin) * (colEnd - colBegin);
+  if (nRecords) *nRecords = n;
+  if (!out || capRecords < n) return fail(c, HAVAC_CUDA_E_LENGTH, "record buffer too small: " + std::to_string(n) + " cells");
+  // a diagonal of the window starts rowEnd - 1 columns to its left at most; those symbols must be resident
+  if ((long long)colBegin - (long long)(rowEnd - 1) < d.resBegin && d.resBegin > 0)
+    return fail(c, HAVAC_CUDA_E_LENGTH, "trace window needs symbols left of the resident range");
+  CK(cudaSetDevice(d.dev));
+  SsvParams p{};
+  p.seqPacked = d.dSeq;
+  p.nLoad = d.resEnd - d.resBegin;
+  p.loadBegin = d.resBegin;
+  p.tab8 = d.dTab8;
+  p.nRows = c->nRows;
+  SsvCellRecord* dOut = nullptr;
+  CK(cudaMalloc(&dOut, n * sizeof(SsvCellRecord)));
+  ssv_launch_trace(p, rowBegin, rowEnd, (long long)colBegin - d.resBegin, (long long)colEnd - d.resBegin, dOut, d.stream);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out, dOut, n * sizeof(SsvCellRecord), cudaMemcpyDeviceToHost, d.stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(d.stream);
+  cudaFree(dOut);
+  if (e != cudaSuccess) return fail(c, HAVAC_CUDA_E_RUNTIME, std::string("trace_cells: ") + cudaGetErrorString(e));
+  c->d2hBytes += n * sizeof(SsvCellRecord);
+  return HAVAC_CUDA_OK;
+}
+
+int havac_cuda_debug_poke_phmm(havac_cuda_client* c, uint64_t byteOffset, int8_t value) {
+  if (!c) return HAVAC_CUDA_E_INVALID;
+  if (c->launched && !c->finished) return fail(c, HAVAC_CUDA_E_LOGIC, "a run is in flight");
+  if (byteOffset >= (uint64_t)c->nRows * 4) return fail(c, HAVAC_CUDA_E_LENGTH, "offset beyond the resident score table");
+  for (DeviceCtx& d : c->devs) {
+    CK(cudaSetDevice(d.dev));
+    CK(cudaMemcpyAsync(d.dTab8 + byteOffset, &value, 1, cudaMemcpyHostToDevice, d.stream));
+    ssv_launch_table_prep(d.dTab8, c->nRows, d.dTab16, d.rowsPadded, d.stream);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(d.stream));
+  }
+  return HAVAC_CUDA_OK;
+}
+
 int havac_cuda_cell_selftest(havac_cuda_client* c, uint8_t* score, uint8_t* hit) {
   if (!c || !score || !hit) return HAVAC_CUDA_E_INVALID;
   DeviceCtx& d = c->devs[0];

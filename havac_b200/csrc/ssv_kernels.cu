@@ -145,6 +145,43 @@ __global__ void ssv_scalar_kernel(SsvParams prm) {
   }
 }
 
+// Per-cell trace (the reference's HAVAC_PER_CELL_DATA_TESTING mode, device/PublicDefines.h:11): one thread per
+// diagonal that crosses the window, run from its first row with the plain kernel's arithmetic on what the
+// DEVICE holds (packed symbols, int8 table), writing a record for every cell inside the window.
+__global__ void ssv_trace_kernel(SsvParams prm, uint32_t rowBegin, uint32_t rowEnd, long long colBegin, long long colEnd,
+                                 SsvCellRecord* __restrict__ out) {
+  // diagonals (local column - row) that have a cell in the window: [colBegin - (rowEnd - 1), colEnd - rowBegin)
+  const long long dFirst = colBegin - (long long)(rowEnd - 1);
+  const long long nDiag = (colEnd - (long long)rowBegin) - dFirst;
+  const long long width = colEnd - colBegin;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < nDiag; t += (long long)gridDim.x * blockDim.x) {
+    const long long d = dFirst + t;  // in columns of the loaded range
+    int s = 0;
+    for (uint32_t p = d < 0 ? (uint32_t)(-d) : 0u; p < rowEnd; p++) {
+      const long long j = d + p;
+      if (j >= prm.nLoad) break;
+      const uint32_t x = (prm.seqPacked[j >> 4] >> ((j & 15) * 2)) & 3;
+      const int e = prm.tab8[4 * (size_t)p + x];
+      const int prev = s;
+      bool hit = false;
+      s += e;
+      if (s < 0) s = 0;
+      else if (s >= 256) { s = 0; hit = true; }
+      if (p >= rowBegin && j >= colBegin && j < colEnd) {
+        SsvCellRecord r;
+        r.prevValue = (uint8_t)prev;
+        r.matchScore = (int8_t)e;
+        r.cellValue = (uint8_t)s;
+        for (int i = 0; i < 4; i++) r.phmmVector[i] = prm.tab8[4 * (size_t)p + i];
+        r.symbol = (uint8_t)x;
+        r.passesThreshold = hit ? 1 : 0;
+        r.pad[0] = r.pad[1] = r.pad[2] = 0;
+        out[(size_t)(p - rowBegin) * width + (j - colBegin)] = r;
+      }
+    }
+  }
+}
+
 }  // namespace
 
 // =======================================================================================
@@ -674,6 +711,15 @@ __global__ void cell_selftest_kernel(uint8_t* __restrict__ outScore, uint8_t* __
 // =======================================================================================
 // launchers
 // =======================================================================================
+void ssv_launch_trace(const SsvParams& prm, uint32_t rowBegin, uint32_t rowEnd, long long colBegin, long long colEnd,
+                      SsvCellRecord* out, void* stream) {
+  const long long nDiag = (colEnd - colBegin) + (long long)(rowEnd - rowBegin) - 1;
+  long long blocks = (nDiag + 127) / 128;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks < 1) blocks = 1;
+  ssv_trace_kernel<<<(int)blocks, 128, 0, (cudaStream_t)stream>>>(prm, rowBegin, rowEnd, colBegin, colEnd, out);
+}
+
 void ssv_launch_cell_selftest(uint8_t* outScore, uint8_t* outHit, void* stream) {
   cell_selftest_kernel<<<256, 256, 0, (cudaStream_t)stream>>>(outScore, outHit);
 }

@@ -34,6 +34,17 @@ struct SsvParams {
 
 enum : int { SSV_STATUS_OVERFLOW = 1, SSV_STATUS_ABORTED = 2 };
 
+// One cell of the per-cell trace: the fields of test/byCellComparator/byCellComparator.hpp:23-31 (12 bytes).
+struct SsvCellRecord {
+  uint8_t prevValue;
+  int8_t matchScore;
+  uint8_t cellValue;
+  int8_t phmmVector[4];
+  uint8_t symbol;
+  uint8_t passesThreshold;
+  uint8_t pad[3];
+};
+
 // Kernel geometry of the fast path (see ssv_kernels.cu).
 constexpr int SSV_R = 16;            // fp16x2 state registers per thread (2 diagonals each)
 #ifndef SSV_THREADS_V
@@ -58,6 +69,8 @@ void ssv_launch_project_table(const float* emissions, uint32_t nRows, const uint
                               uint32_t nModels, int8_t* tab8, void* stream);
 void ssv_launch_f16x2(const SsvParams& prm, int numSMs, void* stream);
 void ssv_launch_scalar(const SsvParams& prm, void* stream);
+void ssv_launch_trace(const SsvParams& prm, uint32_t rowBegin, uint32_t rowEnd, long long colBegin, long long colEnd,
+                      SsvCellRecord* out, void* stream);
 int ssv_f16x2_ctas_per_sm();
 // 2 x 65536 bytes each: plane 0 = the low fp16 half's result for pair i = prev * 256 + (e + 128), plane 1 = the high half's
 void ssv_launch_cell_selftest(uint8_t* outScore, uint8_t* outHit, void* stream);

@@ -171,6 +171,26 @@ int havac_cuda_run_stats(havac_cuda_client* c, uint64_t* cells, uint32_t* launch
 int havac_cuda_sm_cycles(havac_cuda_client* c, uint64_t* cycles);
 /* Running totals of the bytes this client copied host->device and device->host. */
 int havac_cuda_transfer_stats(havac_cuda_client* c, uint64_t* h2dBytes, uint64_t* d2hBytes);
+/* Per-cell debug trace: the reference's HAVAC_PER_CELL_DATA_TESTING mode (device/PublicDefines.h:11; record
+ * schema of test/byCellComparator/byCellComparator.hpp:23-31) for a window of the matrix. Runs the plain integer
+ * recurrence on what the (single) device holds -- its packed symbols, its int8 table -- and writes one record per
+ * cell with row in [rowBegin, rowEnd) and global column in [colBegin, colEnd), row-major. For triage of a parity
+ * failure: tests/oracle_lib.py walks these against the CPU oracle's records and names the first cell that differs. */
+typedef struct havac_cuda_cell_record {
+  uint8_t prevValue;
+  int8_t matchScore;
+  uint8_t cellValue;
+  int8_t phmmVector[4];
+  uint8_t symbol;
+  uint8_t passesThreshold;
+  uint8_t pad[3];
+} havac_cuda_cell_record;
+int havac_cuda_trace_cells(havac_cuda_client* c, uint32_t rowBegin, uint32_t rowEnd, uint64_t colBegin, uint64_t colEnd,
+                           havac_cuda_cell_record* out, uint64_t capRecords, uint64_t* nRecords);
+/* Debug: overwrite one byte of the score table AS THE DEVICE HOLDS IT (every device of the client) and rebuild the
+ * fast path's fp16 rows from it. The host's copy is untouched -- this is how the tests stage "device and host
+ * disagree" for the trace above. */
+int havac_cuda_debug_poke_phmm(havac_cuda_client* c, uint64_t byteOffset, int8_t value);
 /* The fast kernel's cell update on all 65,536 (previous score 0..255, emission -128..127) pairs, one launch:
  * score[i] / hit[i] for pair i = prev * 256 + (emission + 128) computed in the low fp16 half, score[65536 + i] /
  * hit[65536 + i] the same pair computed in the high half. hit bit 7 set = the kernel's own overflow test disagreed

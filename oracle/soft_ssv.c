@@ -62,6 +62,54 @@ int64_t oracle_soft_ssv(const uint8_t *symbols, uint64_t n_symbols,
     return found;
 }
 
+/* Per-cell record of the recurrence over a window of the matrix: the fields the reference's
+ * per-cell debug mode stores for every cell (test/byCellComparator/byCellComparator.hpp:23-31,
+ * filled at test/softSsv/SoftSsv.cpp:52-58 under HAVAC_PER_CELL_DATA_TESTING). The whole matrix
+ * is walked as in oracle_soft_ssv (the window's cells depend on everything above-left of it);
+ * cells with row in [row_begin, row_end) and column in [col_begin, col_end) are written row-major. */
+typedef struct {
+    uint8_t prevValue;
+    int8_t matchScore;
+    uint8_t cellValue;
+    int8_t phmmVector[4];
+    uint8_t symbol;
+    uint8_t passesThreshold;
+    uint8_t pad[3];
+} oracle_cell_record;
+
+int64_t oracle_trace_cells(const uint8_t *symbols, uint64_t n_symbols, const int8_t *table, uint64_t n_rows,
+                           uint64_t row_begin, uint64_t row_end, uint64_t col_begin, uint64_t col_end,
+                           oracle_cell_record *out)
+{
+    if (row_end > n_rows || col_end > n_symbols || row_begin > row_end || col_begin > col_end) return -2;
+    uint8_t *row = (uint8_t *)calloc(n_symbols ? n_symbols : 1, 1);
+    if (!row) return -1;
+    const uint64_t width = col_end - col_begin;
+    for (uint64_t p = 0; p < row_end; p++) {
+        const int8_t *e = table + 4 * p;
+        for (int64_t i = (int64_t)n_symbols - 1; i >= 0; i--) {
+            int32_t prev = (i == 0) ? 0 : row[i - 1];
+            int32_t v = prev + (int32_t)e[symbols[i]];
+            int hit = 0;
+            if (v < 0) v = 0;
+            else if (v >= 256) { v = 0; hit = 1; }
+            if (p >= row_begin && (uint64_t)i >= col_begin && (uint64_t)i < col_end) {
+                oracle_cell_record *r = out + (p - row_begin) * width + ((uint64_t)i - col_begin);
+                r->prevValue = (uint8_t)prev;
+                r->matchScore = e[symbols[i]];
+                r->cellValue = (uint8_t)v;
+                memcpy(r->phmmVector, e, 4);
+                r->symbol = symbols[i];
+                r->passesThreshold = (uint8_t)hit;
+                memset(r->pad, 0, 3);
+            }
+            row[i] = (uint8_t)v;
+        }
+    }
+    free(row);
+    return (int64_t)((row_end - row_begin) * width);
+}
+
 /* The same recurrence evaluated the way the FPGA cell does it, with a 9-bit
  * sum and the carry/sign trick (device/HavacHls.cpp:370-402). Used by the
  * oracle self-test to show the two formulations agree on all 65536 inputs. */

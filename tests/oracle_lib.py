@@ -48,6 +48,8 @@ def oracle():
         L.oracle_resolve_hit.argtypes = [C.c_uint64, _u64p, C.c_uint64, _u32p, C.c_uint32,
                                          C.POINTER(C.c_uint64), C.POINTER(C.c_uint32),
                                          C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+        L.oracle_trace_cells.restype = C.c_int64
+        L.oracle_trace_cells.argtypes = [_u8p, C.c_uint64, _i8p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p]
         L.oracle_cell_processor.argtypes = [C.c_uint8, C.c_int8, C.POINTER(C.c_uint8), C.POINTER(C.c_int)]
         L.oracle_gumbel_invsurv.restype = C.c_double
         L.oracle_gumbel_invsurv.argtypes = [C.c_double, C.c_double, C.c_double]
@@ -309,3 +311,40 @@ def check_hits_by_replay(packed, table, raw_hits, n_hit_diagonals, n_random_diag
             assert got == by_diag.get(d, set()), f"edge diagonal {d} (tile offset {(d - geom['loadBegin'] - geom['diagBegin']) % geom['tileDiagonals']})"
             checked += 1
     return checked
+
+
+# ---- per-cell triage (the reference's byCellComparator) ---------------------------------------
+
+def trace_cells(symbols, table, row_begin, row_end, col_begin, col_end):
+    """The CPU oracle's per-cell records of a window (oracle_trace_cells; fields of byCellComparator.hpp:23-31)."""
+    from havac_b200.client import CELL_RECORD
+    L = oracle()
+    symbols = np.ascontiguousarray(symbols, dtype=np.uint8)
+    flat = np.ascontiguousarray(table, dtype=np.int8).reshape(-1)
+    out = np.zeros((row_end - row_begin, col_end - col_begin), dtype=CELL_RECORD)
+    n = L.oracle_trace_cells(symbols, len(symbols), flat, len(flat) // 4, row_begin, row_end, col_begin, col_end, out.ctypes.data)
+    if n != out.size:
+        raise RuntimeError(f"oracle_trace_cells failed: {n}")
+    return out
+
+
+def first_differing_cell(device_records, oracle_records, row_begin=0, col_begin=0):
+    """Walks the two record windows the way compareCellMaps does (test/byCellComparator/byCellComparator.cpp:47-96:
+    sequence index outer, model index inner) and returns None when every cell agrees, else
+    (phmmIndex, globalSequenceIndex, message naming the fields that differ)."""
+    fields = ("prevValue", "matchScore", "cellValue", "phmmVector", "symbol", "passesThreshold")
+    diff = np.zeros(device_records.shape, dtype=bool)
+    for f in fields:
+        d = device_records[f] != oracle_records[f]
+        diff |= d.any(axis=-1) if d.ndim == 3 else d
+    if not diff.any():
+        return None
+    cols = np.flatnonzero(diff.any(axis=0))
+    j = int(cols[0])
+    p = int(np.flatnonzero(diff[:, j])[0])
+    hw, sw = device_records[p, j], oracle_records[p, j]
+    what = [f for f in fields if np.any(hw[f] != sw[f])]
+    show = lambda r: ", ".join(f"{f}={r[f].tolist() if f == 'phmmVector' else int(r[f])}" for f in fields)
+    msg = (f"TEST FAIL: cell (phmmIndex {row_begin + p}, sequenceIndex {col_begin + j}) differs in {what}\n"
+           f"\tHW: {show(hw)}\n\tSW: {show(sw)}")
+    return row_begin + p, col_begin + j, msg
