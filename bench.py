@@ -333,24 +333,8 @@ def run_gpu(args, rank, world, local_rank):
         return float(t.item())
 
     def gather_hits(h):
-        """Every rank's (device-sorted) hit list to rank 0 through host memory; ranks hold increasing segment
-        ranges, so rank order is emission order. Returns (list on rank 0 or None, bytes moved to rank 0)."""
-        if dist is None:
-            return h, 0
-        counts = [None] * world
-        dist.all_gather_object(counts, int(len(h)), group=gloo)
-        if rank != 0:
-            if len(h):
-                dist.send(torch.from_numpy(h.view(np.int64)), dst=0, group=gloo)
-            return None, 0
-        out = np.empty(sum(counts), dtype=np.uint64)
-        out[: counts[0]] = h
-        at = counts[0]
-        for r in range(1, world):
-            if counts[r]:
-                dist.recv(torch.from_numpy(out[at: at + counts[r]].view(np.int64)), src=r, group=gloo)
-            at += counts[r]
-        return out, 8 * (len(out) - counts[0])
+        """One hit list on rank 0 (sharding.gather_hit_lists: host memory, rank order = emission order)."""
+        return sharding.gather_hit_lists(h, rank, world, gloo)
 
     t_setup = time.perf_counter()
     packed, table, n_total, lengths = build_workload(world)

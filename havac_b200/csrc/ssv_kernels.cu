@@ -35,6 +35,7 @@
 //  * Hits are compacted with warp ballot + prefix popcount and one atomicAdd per warp-row.
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdint>
 
 #include "ssv_kernels.cuh"
@@ -221,7 +222,9 @@ struct __align__(16) FastSmem {
   uint4 seqStage[2][TC / 64 + 1];  // packed symbols of the chunk after next (cp.async), double buffered
   unsigned long long mbar[2];
   unsigned int nextTile;
-  int abortSeen;
+  // abort flag as seen by thread 0: [0], [1] written before the end-of-chunk barrier of even / odd chunks and read
+  // by everyone after it; [2] written in the tile prologue. A slot is rewritten two barriers after it was read.
+  int abortSeen[3];
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -534,16 +537,20 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
     mbar_init(&sm.mbar[0], 1);
     mbar_init(&sm.mbar[1], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    sm.abortSeen = 0;
+    sm.abortSeen[0] = sm.abortSeen[1] = sm.abortSeen[2] = 0;
     sm.nextTile = atomicAdd(prm.tileCounter, 1u);
   }
   __syncthreads();
+  bool aborted = false;
 
   while (true) {
-    const unsigned tile = sm.nextTile;
-    const bool aborted = sm.abortSeen != 0;
+    const unsigned ticket = sm.nextTile;
     __syncthreads();  // everyone has read nextTile before thread 0 overwrites it
-    if (tile >= prm.nTiles || aborted) break;
+    if (ticket >= prm.nTiles) break;
+    // Tiles are handed out from the right end of the band to the left: the tiles that start left of column 0
+    // (an unsharded run has rows/W of them, each with fewer rows than the one before) come last and in decreasing
+    // length, which is the order that evens out the finish times of the persistent CTAs.
+    const unsigned tile = prm.nTiles - 1u - ticket;
 
     const long long D0 = prm.diagBegin + (long long)tile * W;  // first diagonal of this tile
     const long long d0 = D0 + (long long)tid * (2 * R);        // first diagonal of this thread
@@ -564,7 +571,7 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
     // --- prologue: queue the first two table chunks, fill the ring, load the windows --------
     if (tid == 0) {
       sm.nextTile = atomicAdd(prm.tileCounter, 1u);
-      if (*prm.abortFlag) sm.abortSeen = 1;
+      sm.abortSeen[2] = *prm.abortFlag;
       for (int i = 0; i < 2 && c0 + i < c1; i++) {
         mbar_expect_tx(&sm.mbar[i], TC * sizeof(uint2));
         tma_load_1d(sm.tab[i], prm.tab16 + (size_t)(c0 + i) * TC, TC * sizeof(uint2), &sm.mbar[i]);
@@ -580,6 +587,11 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
         ring_fill64(sm, p0 + 64u * (uint32_t)i, load_seq_vec(prm, wFill0 + 4 * i), load_seq_word(prm, wFill0 + 4 * i + 4));
     }
     __syncthreads();
+    aborted = sm.abortSeen[2] != 0;  // CTA-uniform: written before the barrier above
+    if (aborted) {  // drain the table chunks queued above, then leave
+      for (int i = 0; i < 2 && c0 + i < c1; i++) mbar_wait(&sm.mbar[i], (mbarPhase >> i) & 1u);
+      break;
+    }
 
     uint32_t w[R], e0[R], e1[R];
     uint32_t g = ((uint32_t)tid + p0 / 32u) % (uint32_t)NSLOT;  // slot of symbol offset 32 tid + p0
@@ -654,22 +666,26 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
       }
 
       asm volatile("cp.async.wait_group 0;" ::: "memory");
+      if (tid == 0 && *prm.abortFlag) sm.abortSeen[c & 1] = 1;  // before the barrier: every thread reads the same value after it
       __syncthreads();  // all reads of tab[buf] and of the ring part about to be recycled are done; seqStage[buf] landed
-      if (tid == 0) {
-        if (c + 2 < c1) {
-          mbar_expect_tx(&sm.mbar[buf], TC * sizeof(uint2));
-          tma_load_1d(sm.tab[buf], prm.tab16 + (size_t)(c + 2) * TC, TC * sizeof(uint2), &sm.mbar[buf]);
-        }
-        if (*prm.abortFlag) sm.abortSeen = 1;
+      aborted = aborted || sm.abortSeen[c & 1] != 0;
+      // the table buffers of a tile that stops here are not refilled: no TMA may be in flight when the CTA exits
+      if (tid == 0 && !aborted && c + 2 < c1) {
+        mbar_expect_tx(&sm.mbar[buf], TC * sizeof(uint2));
+        tma_load_1d(sm.tab[buf], prm.tab16 + (size_t)(c + 2) * TC, TC * sizeof(uint2), &sm.mbar[buf]);
+      }
+      if (aborted) {
+        // chunk c+1 (if any) was queued two chunks ago: wait for it, so that nothing is in flight at exit
+        if (c + 1 < c1) mbar_wait(&sm.mbar[buf ^ 1], (mbarPhase >> (buf ^ 1)) & 1u);
+        break;
       }
       if (doRefill && tid < TC / 64)
         ring_fill64(sm, sRefill + 64u * (uint32_t)tid, sm.seqStage[buf][tid], sm.seqStage[buf][tid + 1].x);
-      if (sm.abortSeen) break;  // uniform: written before the barrier of the previous chunk
     }
     __syncthreads();
-    if (sm.abortSeen) break;
+    if (aborted) break;
   }
-  if (tid == 0 && sm.abortSeen) atomicOr(prm.status, SSV_STATUS_ABORTED);
+  if (tid == 0 && aborted) atomicOr(prm.status, SSV_STATUS_ABORTED);
   if (tid == 0 && blockIdx.x == 0) *prm.smCycles = (unsigned long long)(clock64() - clk0);
 }
 
@@ -737,26 +753,29 @@ void ssv_launch_project_table(const float* emissions, uint32_t nRows, const uint
       reinterpret_cast<uint32_t*>(tab8));
 }
 
-static bool f16x2_prepare() {
-  // the kernel needs more than the 48 KB of shared memory a launch gets by default
-  static int done = -1;  // per process; every device of this process runs the same image
+// The kernels need more than the 48 KB of shared memory a launch gets by default. Function attributes are per
+// DEVICE, so they are set (and the occupancy asked for) once per device ordinal of this process and remembered:
+// a search that lasts microseconds must not pay five runtime calls per launch.
+int ssv_f16x2_ctas_per_sm() {
+  constexpr int MAX_DEV = 64;
+  static std::atomic<int> cached[MAX_DEV];  // 0 = not asked yet
   int dev = 0;
   cudaGetDevice(&dev);
+  if (dev >= 0 && dev < MAX_DEV) {
+    const int have = cached[dev].load(std::memory_order_acquire);
+    if (have > 0) return have;
+  }
   cudaError_t e = cudaSuccess;
   for (auto kernel : {ssv_f16x2_kernel, ssv_f16x2_tail_kernel}) {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem));
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   }
-  done = (e == cudaSuccess);
-  return done == 1;
-}
-
-int ssv_f16x2_ctas_per_sm() {
   int n = 0;
-  f16x2_prepare();
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, ssv_f16x2_kernel, THREADS, sizeof(FastSmem));
-  return n > 0 ? n : 1;
+  if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, ssv_f16x2_kernel, THREADS, sizeof(FastSmem));
+  if (e != cudaSuccess || n < 1) return 1;  // not remembered: the launch that follows reports the error
+  if (dev >= 0 && dev < MAX_DEV) cached[dev].store(n, std::memory_order_release);
+  return n;
 }
 
 void ssv_launch_f16x2(const SsvParams& prm, int numSMs, void* stream) {

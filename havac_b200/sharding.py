@@ -48,3 +48,30 @@ def merge_hits(parts: Sequence[np.ndarray]) -> np.ndarray:
         return np.zeros(0, dtype=np.uint64)
     allhits = np.concatenate(parts)
     return allhits[np.argsort(emission_order_key(allhits), kind="stable")]
+
+
+def gather_hit_lists(hits: np.ndarray, rank: int, world_size: int, group=None):
+    """Every rank's hit list to rank 0 through HOST memory (a gloo group; the lists never go back to a GPU).
+    Each rank's list is already in emission order (the device sorts it) and ranks hold increasing segment ranges,
+    so laying the lists end to end in rank order IS the global emission order -- no merge on rank 0.
+    Returns (the whole list on rank 0 / None elsewhere, bytes received by rank 0)."""
+    import torch
+    import torch.distributed as dist
+
+    hits = np.ascontiguousarray(hits, dtype=np.uint64)
+    if world_size == 1:
+        return hits, 0
+    counts = [None] * world_size
+    dist.all_gather_object(counts, int(len(hits)), group=group)
+    if rank != 0:
+        if len(hits):
+            dist.send(torch.from_numpy(hits.view(np.int64)), dst=0, group=group)
+        return None, 0
+    out = np.empty(sum(counts), dtype=np.uint64)
+    out[: counts[0]] = hits
+    at = counts[0]
+    for r in range(1, world_size):
+        if counts[r]:
+            dist.recv(torch.from_numpy(out[at: at + counts[r]].view(np.int64)), src=r, group=group)
+        at += counts[r]
+    return out, 8 * (len(out) - counts[0])

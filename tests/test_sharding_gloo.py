@@ -55,11 +55,18 @@ def _worker(rank, world, port, out_path):
     mine = O.encode_hits(pos[keep], row[keep])
     gathered = [None] * world if rank == 0 else None
     dist.gather_object(mine, gathered, dst=0)
+    # the gather bench.py's e2e leg ends with: each rank's list sorted into emission order (the device does that),
+    # sent to rank 0 through host memory and laid end to end -- which must already BE the merged order
+    mine_sorted = sharding.merge_hits([mine])
+    whole_on_0, moved = sharding.gather_hit_lists(mine_sorted, rank, world)
     if rank == 0:
         merged = sharding.merge_hits(gathered)
+        assert np.array_equal(whole_on_0, merged) and moved == 8 * (len(merged) - len(mine))
         wp, wr = O.soft_ssv(allsym, table)
         whole = sharding.merge_hits([O.encode_hits(wp, wr)])
         np.savez(out_path, merged=merged, whole=whole, per_rank=np.array([len(g) for g in gathered]))
+    else:
+        assert whole_on_0 is None and moved == 0
     dist.barrier()
     dist.destroy_process_group()
 

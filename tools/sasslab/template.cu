@@ -11,7 +11,7 @@
 #ifndef NREG
 #define NREG 96
 #endif
-extern "C" __global__ void __launch_bounds__(128, 4) ub(uint32_t* out, long long* cycles, int iters) {
+extern "C" __global__ void __launch_bounds__(512, 1) ub(uint32_t* out, long long* cycles, int iters) {
   uint32_t r[NREG];
   const uint32_t t = threadIdx.x * 2654435761u + blockIdx.x;
 #pragma unroll
