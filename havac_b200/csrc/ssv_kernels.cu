@@ -474,22 +474,29 @@ template <int U>
 __device__ __forceinline__ void four_rows(uint32_t (&w)[R], uint32_t (&e0)[R], uint32_t (&e1)[R],
                                           const uint2* __restrict__ tabRow,
                                           const uint4* __restrict__ ringSlot) {
-  const uint4 win = ringSlot[U * NSLOT];                                    // windows of the next block
+  // The four new windows are fetched as two 64-bit halves: a half can be loaded IN PLACE over the two windows that
+  // die in rows 4U and 4U+1 (resp. 4U+2 and 4U+3) two rows before its first use, which is what lets the block
+  // scheduler (havac_b200/sass/reblock.py) keep every window in one register for the whole block.
+  // (ld.volatile: ptxas fuses two adjacent plain 64-bit loads, inline asm or not, back into one LDS.128.)
+  const uint32_t ringAddr = smem_u32(ringSlot + U * NSLOT);
+  uint2 win01, win23;  // windows of the next block: rows 4U, 4U+1 and rows 4U+2, 4U+3
+  asm volatile("ld.volatile.shared.v2.u32 {%0, %1}, [%2];" : "=r"(win01.x), "=r"(win01.y) : "r"(ringAddr));
+  asm volatile("ld.volatile.shared.v2.u32 {%0, %1}, [%2+8];" : "=r"(win23.x), "=r"(win23.y) : "r"(ringAddr));
   const uint4 ab01 = *reinterpret_cast<const uint4*>(tabRow + 4 * U);      // rows 4U, 4U+1
   const uint4 ab23 = *reinterpret_cast<const uint4*>(tabRow + 4 * U + 2);  // rows 4U+2, 4U+3
   constexpr int Q0 = 2 * U, Q1 = 2 * U + 1;
 #pragma unroll
   for (int k = 0; k < R; k++) w[k] = hfma2_relu_add(prmt(ab01.x, ab01.y, e0[(Q0 + k) % R]), w[k]);
-  e0[Q0 % R] = win.x;
+  e0[Q0 % R] = win01.x;
 #pragma unroll
   for (int k = 0; k < R; k++) w[k] = hfma2_relu_add(prmt(ab01.z, ab01.w, e1[(Q0 + k) % R]), w[k]);
-  e1[Q0 % R] = win.y;
+  e1[Q0 % R] = win01.y;
 #pragma unroll
   for (int k = 0; k < R; k++) w[k] = hfma2_relu_add(prmt(ab23.x, ab23.y, e0[(Q1 + k) % R]), w[k]);
-  e0[Q1 % R] = win.z;
+  e0[Q1 % R] = win23.x;
 #pragma unroll
   for (int k = 0; k < R; k++) w[k] = hfma2_relu_add(prmt(ab23.z, ab23.w, e1[(Q1 + k) % R]), w[k]);
-  e1[Q1 % R] = win.w;
+  e1[Q1 % R] = win23.y;
 }
 
 template <int U>
