@@ -1,6 +1,12 @@
 """In-tree builds: the CUDA device client (libhavac_cuda.so, sm_100a only) and the host-side
 C++ driver (libhavac_host.so). nvcc cross-compiles without a GPU. Artefacts land in
-havac_b200/lib/ so they travel to the GPU box with the repo snapshot."""
+havac_b200/lib/ so they travel to the GPU box with the repo snapshot.
+
+The SSV kernels take one step more than `nvcc -c`: after ptxas has produced the cubin, the unrolled row block of the
+fast kernels is re-scheduled at SASS level (havac_b200/sass/reblock.py -- order, temporaries, .reuse flags and
+scheduling-control bits that neither CUDA C++ nor PTX can pin; +25 % on the B200), and the object is finished from
+the patched cubin with nvcc's own fatbinary / host-compile commands. HAVAC_NO_REBLOCK=1 skips that step (the
+library then carries ptxas's schedule; used for A/B measurements)."""
 from __future__ import annotations
 
 import os
@@ -18,8 +24,10 @@ INCLUDE = os.path.join(ROOT, "include")
 CUDA_LIB = os.path.join(LIB, "libhavac_cuda.so")
 HOST_LIB = os.path.join(LIB, "libhavac_host.so")
 
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-              "-Xcompiler", "-fPIC", "-shared", "-cudart", "static"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC"]
+NVCC_LINK_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-cudart", "static", "-Xcompiler", "-fPIC"]
+OBJ_DIR = os.path.join(ROOT, "build", "cuda")
+RESCHEDULED = "ssv_kernels.cu"  # the translation unit whose cubin goes through havac_b200/sass/reblock.py
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-fno-fast-math", "-Wall"]
 
 
@@ -41,16 +49,65 @@ def _sources(directory: str, exts) -> list:
     return sorted(os.path.join(directory, f) for f in os.listdir(directory) if f.endswith(tuple(exts)))
 
 
-def build_cuda(force: bool = False, verbose: bool = False) -> str:
+def _compile_rescheduled(nvcc, cu, obj, work, defines, verbose):
+    """nvcc -c with the cubin patched between ptxas and fatbinary. The command lines of the two steps that follow
+    ptxas are nvcc's own (taken from `nvcc -dryrun --keep`), re-run after the patch."""
+    from havac_b200.sass import reblock
+
+    os.makedirs(work, exist_ok=True)
+    base = [nvcc, "--keep", "--keep-dir", work, *NVCC_FLAGS, *defines, "-I", INCLUDE, "-c", "-o", obj, cu]
+    dry = subprocess.run(base[:1] + ["-dryrun"] + base[1:], check=True, capture_output=True, text=True).stderr.splitlines()
+    env = dict(os.environ)
+    steps = []
+    for line in dry:
+        if not line.startswith("#$ "):
+            continue
+        line = line[3:]
+        m = __import__("re").match(r"^([A-Za-z_][A-Za-z0-9_]*)=(.*)$", line)
+        if m and " " not in m.group(1) and not line.startswith(("gcc", "ptxas", "fatbinary", "cicc", "cudafe", "rm", '"')):
+            env[m.group(1)] = os.path.expandvars(m.group(2).strip()) if m.group(1) != "PATH" else m.group(2).strip()
+        else:
+            steps.append(line)
+    env["PATH"] = env.get("PATH", "") + os.pathsep + os.environ.get("PATH", "")
+    subprocess.run(base + (["-Xptxas=-v"] if verbose else []), check=True)
+    cubin = os.path.join(work, os.path.basename(cu)[:-3] + ".cubin")
+    report = reblock.patch_cubin(cubin, cubin, verbose=verbose)
+    done = [(k, v) for k, v in report.items() for b in v if b[2] == "rescheduled"]
+    if not done:
+        raise RuntimeError(f"reblock: no block of {cu} could be re-scheduled: {report}")
+    after = [c for c in steps[next(n for n, c in enumerate(steps) if c.startswith("ptxas")) + 1:] if not c.startswith("rm ")]
+    for c in after:
+        subprocess.run(c, shell=True, check=True, env=env, cwd=work, executable="/bin/bash")
+    return report
+
+
+def build_cuda(force: bool = False, verbose: bool = False, out: str = None, reblock: bool = None, defines=()) -> str:
+    """libhavac_cuda.so (or a variant at `out`): every .cu compiled to an object, the SSV kernels' cubin re-scheduled
+    on the way (unless reblock=False / HAVAC_NO_REBLOCK=1), then linked."""
     os.makedirs(LIB, exist_ok=True)
+    target = out or CUDA_LIB
+    if reblock is None:
+        reblock = os.environ.get("HAVAC_NO_REBLOCK") != "1"
     cu = _sources(CSRC, (".cu",))
-    deps = cu + _sources(CSRC, (".cuh",)) + _sources(INCLUDE, (".h",))
-    if force or _stale(CUDA_LIB, deps):
-        cmd = [_nvcc(), *NVCC_FLAGS, "-I", INCLUDE, "-o", CUDA_LIB, *cu]
-        if verbose:
-            cmd.insert(1, "-Xptxas=-v")
-        subprocess.run(cmd, check=True)
-    return CUDA_LIB
+    deps = cu + _sources(CSRC, (".cuh",)) + _sources(INCLUDE, (".h",)) + _sources(os.path.join(PKG, "sass"), (".py",)) + [__file__]
+    if force or out or _stale(target, deps):
+        nvcc = _nvcc()
+        tag = os.path.basename(target).replace(".so", "")
+        work = os.path.join(OBJ_DIR, tag)
+        os.makedirs(work, exist_ok=True)
+        objs = []
+        for src in cu:
+            obj = os.path.join(work, os.path.basename(src)[:-3] + ".o")
+            if reblock and os.path.basename(src) == RESCHEDULED:
+                _compile_rescheduled(nvcc, src, obj, os.path.join(work, "keep"), list(defines), verbose)
+            else:
+                cmd = [nvcc, *NVCC_FLAGS, *defines, "-I", INCLUDE, "-c", "-o", obj, src]
+                if verbose:
+                    cmd.insert(1, "-Xptxas=-v")
+                subprocess.run(cmd, check=True)
+            objs.append(obj)
+        subprocess.run([nvcc, *NVCC_LINK_FLAGS, "-o", target, *objs], check=True)
+    return target
 
 
 def build_host(force: bool = False) -> str:

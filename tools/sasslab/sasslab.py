@@ -186,7 +186,45 @@ def stream_ratio(enc, R, n_p, n_h):
     return out[:NBODY]
 
 
+def stream_real(enc, pool, a_par=0, c_par=1, w_mode="alt", m_mode="opp", sel_mode="row", lag=3):
+    """The production block's shape (havac_b200/sass/reblock.py): lookups row-major, updates IN PLACE `lag` pairs behind,
+    strict alternation; table pair (a, c) of a row with the given register parities and .reuse on all but the row's last
+    lookup; state register of chain k of parity k % 2 ("alt") or fixed; lookup temporary of the opposite / same / fixed
+    parity; selector of the row's parity ("row": even rows read even registers) or fixed."""
+    ev = [r for r in pool if r % 2 == 0]
+    od = [r for r in pool if r % 2 == 1]
+    take = {0: iter(ev), 1: iter(od)}
+    tabs = [(next(take[a_par]), next(take[c_par])) for _ in range(4)]
+    wpar = [{"alt": k % 2, "even": 0, "odd": 1}[w_mode] for k in range(16)]
+    w = [next(take[p]) for p in wpar]
+    mpar = [{"opp": 1 - wpar[k], "same": wpar[k], "even": 0, "odd": 1}[m_mode] for k in range(16)]
+    m = [next(take[p]) for p in mpar]
+    sel = {0: [next(take[0]) for _ in range(12)], 1: [next(take[1]) for _ in range(12)]}
+    N = NBODY // 2
+    out = []
+    for i in range(N):
+        r, k = i // 16, i % 16
+        a, c = tabs[r % 4]
+        sp = {"row": r % 2, "even": 0, "odd": 1}[sel_mode]
+        ru = k != 15
+        out.append(enc.prmt(m[k], a, sel[sp][(r // 2 + k) % 12], c, reuse_a=ru, reuse_c=ru))
+        kk = (i - lag) % 16  # the loop wraps: the first updates of an iteration consume the last lookups of the one before
+        out.append(enc.hfma2(w[kk], m[kk], w[kk]))
+    return out[:NBODY]
+
+
+def experiments2(enc, pool):
+    ex = {}
+    for a_par, c_par in ((0, 1), (1, 0), (0, 0), (1, 1)):
+        for w_mode, m_mode in (("alt", "opp"), ("even", "odd"), ("odd", "even"), ("alt", "same")):
+            for sel_mode in ("row", "even"):
+                ex[f"real_a{a_par}c{c_par}_w{w_mode}_m{m_mode}_sel{sel_mode}"] = stream_real(enc, pool, a_par, c_par, w_mode, m_mode, sel_mode)
+    return ex
+
+
 def experiments(enc, pool):
+    if os.environ.get("SASSLAB_SET") == "2":
+        return experiments2(enc, pool)
     mixed = Regs(pool, "mixed")
     ex = {}
     ex["P_only_reuse"] = stream_only(enc, mixed, "P", True)
@@ -257,7 +295,7 @@ def build():
         manifest[name] = {"prmt": n_p, "hfma2": NBODY - n_p}
     json.dump(manifest, open(os.path.join(OUT, "manifest.json"), "w"), indent=1)
     # a disassembly of two experiments, to check by eye that nvdisasm reads the patched words as intended
-    for name in ("alt_lag3_reuse", "grouped16_reuse"):
+    for name in [n for n in ("alt_lag3_reuse", "grouped16_reuse", "real_a0c1_walt_mopp_selrow") if n in manifest]:
         txt = subprocess.run(["cuobjdump", "-sass", "-fun", "ub", os.path.join(OUT, name + ".cubin")], capture_output=True, text=True).stdout
         open(os.path.join(OUT, name + ".sass"), "w").write(txt)
     print(f"{len(manifest)} experiment cubins in {OUT}")
