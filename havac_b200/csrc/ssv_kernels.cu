@@ -195,11 +195,11 @@ constexpr int THREADS = SSV_THREADS;
 constexpr int W = SSV_TILE_DIAGS;
 constexpr int TC = SSV_ROW_CHUNK;
 constexpr int BLOCK_ROWS = SSV_BLOCK_ROWS;          // rows unrolled in one block (= 2R = 32)
-constexpr int SB_BLOCKS = SSV_SUPERBLOCK_BLOCKS;    // blocks between two hit checks / checkpoints
-constexpr int SB_ROWS = SB_BLOCKS * BLOCK_ROWS;
+// One 32-row block between two checkpoints / hit checks: a replay costs the rows it covers, and two blocks per check
+// measured slower even on hit-free input (profiles/r1_ubench10_row_band.txt; again in round 2 with the re-scheduled block).
 constexpr int NSLOT = (W + 2 * TC) / 32;            // 32-symbol groups the window ring holds
 static_assert(BLOCK_ROWS == 32 && R == 16, "the ring layout assumes 32 diagonals and 32 rows per thread-block");
-static_assert(TC % SB_ROWS == 0, "row chunk must hold whole superblocks");
+static_assert(TC % BLOCK_ROWS == 0, "row chunk must hold whole blocks");
 static_assert(TC % 64 == 0 && TC / 64 <= THREADS, "chunk refill is done by the first TC/64 threads, 64 symbols each");
 static_assert((W + 2 * TC) % 32 == 0, "ring must hold whole 32-symbol groups");
 
@@ -569,6 +569,8 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
     if (rowBegin < 0) rowBegin = 0;
     const int c0 = (int)(rowBegin / TC);
     const int c1 = (int)((rowEnd + TC - 1) / TC);  // exclusive
+    // rows (from row 0) in which the tile still has diagonals left of column 0: D0 + row < 0
+    const uint32_t edgeRows = D0 < 0 ? (uint32_t)(-D0 < 0x7fffffffll ? -D0 : 0x7fffffffll) : 0u;
     if (rowEnd <= rowBegin) {                       // nothing to do (defensive)
       if (tid == 0) sm.nextTile = atomicAdd(prm.tileCounter, 1u);
       __syncthreads();
@@ -630,41 +632,44 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
       mbar_wait(&sm.mbar[buf], (mbarPhase >> buf) & 1u);
       mbarPhase ^= 1u << buf;
 
-      long long chunkEnd = (long long)(c + 1) * TC;
-      if (chunkEnd > rowEnd) chunkEnd = rowEnd;
-      for (uint32_t pb = (uint32_t)c * TC; (long long)pb < chunkEnd; pb += SB_ROWS) {
-        int nb = (int)((chunkEnd - (long long)pb + BLOCK_ROWS - 1) / BLOCK_ROWS);
-        if (nb > SB_BLOCKS) nb = SB_BLOCKS;
+      // Per block of 32 rows: checkpoint, the block, one look at the states. Everything around the block is kept in
+      // 32-bit registers and as short as it can be: these instructions queue for the same (saturated) ALU pipe as the
+      // block's lookups, so each one of them costs two of its clocks.
+      const uint32_t pbEnd = (long long)(c + 1) * TC < rowEnd ? (uint32_t)(c + 1) * TC : (uint32_t)rowEnd;
+      const uint2* tabRow = sm.tab[buf];
+      for (uint32_t pb = (uint32_t)c * TC; pb < pbEnd; pb += BLOCK_ROWS) {
 #pragma unroll
         for (int q = 0; q < R / 4; q++)
           sm.ckpt[q][tid] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
-        const uint2* tabRow = sm.tab[buf] + (pb & (TC - 1));
-#pragma unroll 1
-        for (int b = 0; b < nb; b++) {
-          if constexpr (TAIL) {
-            const int left = (int)(chunkEnd - (long long)pb) - b * BLOCK_ROWS;  // rows of the tile from this block on
-            if (left > 24) RowGroups<0>::run(w, e0, e1, tabRow + b * BLOCK_ROWS, &sm.ring[0][g]);
-            else if (left > 16) RowGroupsTo<0, 6>::run(w, e0, e1, tabRow + b * BLOCK_ROWS, &sm.ring[0][g]);
-            else if (left > 8) RowGroupsTo<0, 4>::run(w, e0, e1, tabRow + b * BLOCK_ROWS, &sm.ring[0][g]);
-            else RowGroupsTo<0, 2>::run(w, e0, e1, tabRow + b * BLOCK_ROWS, &sm.ring[0][g]);
-          } else {
-            RowGroups<0>::run(w, e0, e1, tabRow + b * BLOCK_ROWS, &sm.ring[0][g]);
-          }
-          g = (g + 1 == (uint32_t)NSLOT) ? 0u : g + 1;
+#ifdef SSV_DEBUG_SPLIT_HEAD
+        __syncwarp();
+#endif
+        if constexpr (TAIL) {
+          const uint32_t left = pbEnd - pb;  // rows of the tile from this block on
+          if (left > 24) RowGroups<0>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
+          else if (left > 16) RowGroupsTo<0, 6>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
+          else if (left > 8) RowGroupsTo<0, 4>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
+          else RowGroupsTo<0, 2>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
+        } else {
+          RowGroups<0>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
         }
+        tabRow += BLOCK_ROWS;
+        g = (g + 1 == (uint32_t)NSLOT) ? 0u : g + 1;
+#ifdef SSV_DEBUG_SPLIT_TAIL
+        __syncwarp();
+#endif
 
         // post-pass: hit replay, and the band left of column 0 in the first tiles
-        const uint32_t rows = (uint32_t)nb * BLOCK_ROWS;
         uint32_t mx = 0;
 #pragma unroll
         for (int k = 0; k < R; k += 2) mx = __vimax3_s16x2(mx, w[k], w[k + 1]);
-        const bool edge = D0 + (long long)pb < 0;  // tile-uniform: diagonals left of column 0 remain
+        const bool edge = pb < edgeRows;  // tile-uniform: diagonals left of column 0 remain
         if (edge || __any_sync(FULL, has_inf(mx))) {
           // cold path, out of line: the replay leaves the exact states in the checkpoint slots
           uint32_t infMask = 0;
 #pragma unroll
           for (int k = 0; k < R; k++) infMask |= has_inf(w[k]) ? (1u << k) : 0u;
-          const uint32_t changed = exact_rows(prm, sm, sm.tab[buf], infMask, edge, d0, D0, pb, rows);
+          const uint32_t changed = exact_rows(prm, sm, sm.tab[buf], infMask, edge, d0, D0, pb, BLOCK_ROWS);
           const uint32_t* ck = reinterpret_cast<const uint32_t*>(&sm.ckpt[0][0]);
 #pragma unroll
           for (int k = 0; k < R; k++)

@@ -55,12 +55,8 @@ constexpr int SSV_TILE_DIAGS = SSV_THREADS * 2 * SSV_R;  // 8192
 #ifndef SSV_ROW_CHUNK_V
 #define SSV_ROW_CHUNK_V 2048  // 512 -> 2048 measured +1.9 % (fewer CTA-wide barriers per tile)
 #endif
-#ifndef SSV_SUPERBLOCK_BLOCKS_V
-#define SSV_SUPERBLOCK_BLOCKS_V 1
-#endif
 constexpr int SSV_ROW_CHUNK = SSV_ROW_CHUNK_V;   // rows of the score table staged per TMA bulk copy
 constexpr int SSV_BLOCK_ROWS = 2 * SSV_R;
-constexpr int SSV_SUPERBLOCK_BLOCKS = SSV_SUPERBLOCK_BLOCKS_V;  // 32-row blocks between two hit checks
 
 // host-callable launchers (defined in ssv_kernels.cu); all asynchronous on `stream`.
 void ssv_launch_table_prep(const int8_t* tab8, uint32_t nRows, uint2* tab16, uint32_t rowsPadded,
