@@ -410,9 +410,13 @@ def run_gpu(args, rank, world, local_rank):
     h2d0, d2h0 = client.transferStats()
     barrier()
     t0 = time.perf_counter()
+    step_ms = []
     for _ in range(args.steps):
+        ts = time.perf_counter()
         hits, whole = e2e_step()
+        step_ms.append(round((time.perf_counter() - ts) * 1e3, 2))
     barrier()
+    log(f"[rank {rank}] e2e wall per step (ms): {step_ms}")
     e2e_s = reduce((time.perf_counter() - t0) / args.steps, "MAX")
     h2d1, d2h1 = client.transferStats()
     log(f"[rank {rank}] e2e phases of the last step (ms): {phases}")
