@@ -198,8 +198,10 @@ def execute(seq):
         if x.kind == "P":
             val[x.d] = ("P", v(x.a), v(x.b), v(x.c))
         elif x.kind == "H":
-            # fma(m, 1, w) == fma(w, 1, m) bit for bit: a re-emitted update may carry its operands the other way round
-            val[x.d] = ("H", v(x.c), v(x.a)) if getattr(x, "swap", False) else ("H", v(x.a), v(x.c))
+            # fma(m, 1, w) == fma(w, 1, m) bit for bit: an update may carry its operands either way round (the re-emitted
+            # ones do, by register parity); the value is written lookup first
+            va, vc = v(x.a), v(x.c)
+            val[x.d] = ("H", vc, va) if (vc[0] == "P" and va[0] != "P") else ("H", va, vc)
         elif x.kind == "L":
             lds_addr[x.uid] = tuple(v(r) for r in x.addr_regs)
             for i in range(x.width):

@@ -77,7 +77,7 @@ def main():
           f"PRMT-HFMA2 or HFMA2-PRMT {len(re.findall('(?=PH|HP)', seq))}")
     runs = collections.Counter(len(m.group(0)) for m in re.finditer(r"P+|H+", seq))
     print("# run lengths of same-pipe instructions (length: count):", dict(sorted(runs.items())))
-    prmt = [x for x in blk if x["op"].startswith("PRMT")]
+    prmt = [x for x in blk if x["op"].startswith("PRMT") and len(x["regs"]) == 4]  # (not the "PRMT R, RZ, imm, RZ" that makes a zero)
     hfma = [x for x in blk if x["op"].startswith("HFMA2")]
     both = sum(1 for x in prmt if x["reuse"] & 5 == 5)
     print(f"# PRMT .reuse on both table registers: {both} of {len(prmt)}; on none: {sum(1 for x in prmt if x['reuse'] & 5 == 0)}")
@@ -95,8 +95,8 @@ def main():
         sel = collections.Counter(x["regs"][2] % mod for x in prmt)
         mm = collections.Counter(x["regs"][1] % mod for x in hfma)
         ww = collections.Counter(x["regs"][2] % mod for x in hfma)
-        print(f"# register index mod {mod}: PRMT selector {dict(sorted(sel.items()))}  HFMA2 lookup operand {dict(sorted(mm.items()))}  "
-              f"HFMA2 state operand {dict(sorted(ww.items()))}")
+        print(f"# register index mod {mod}: PRMT selector {dict(sorted(sel.items()))}  HFMA2 first (slot A) operand {dict(sorted(mm.items()))}  "
+              f"HFMA2 last (slot C) operand {dict(sorted(ww.items()))}")
         same = sum(1 for x in hfma if x["regs"][1] % mod == x["regs"][2] % mod)
         print(f"#   HFMA2 with both register operands in one bank (mod {mod}): {same} of {len(hfma)}")
         tri = sum(1 for x in prmt if len({r % mod for r in x["regs"][1:4]}) == 1)
@@ -107,9 +107,9 @@ def main():
     for x in blk:
         at[x["addr"]] = t
         if x["op"].startswith("HFMA2"):
-            src = x["regs"][1]
-            if src in last_def and last_def[src][1].startswith("PRMT"):
-                dist[t - last_def[src][0]] += 1
+            for src in x["regs"][1:]:  # the lookup result is the first or the last operand (fma(m, 1, w) == fma(w, 1, m))
+                if src in last_def and last_def[src][1].startswith("PRMT"):
+                    dist[t - last_def[src][0]] += 1
         if x["regs"] and not x["op"].startswith(("STS", "ST.")):
             last_def[x["regs"][0]] = (t, x["op"])
         t += max(1, x["stall"])
