@@ -13,7 +13,7 @@ constexpr long long SEG = HAVAC_CUDA_SEGMENT_SYMBOLS;
 constexpr unsigned long long MAX_ROWS = 1ull << 24;  // phmmPos_t is 24 bits (device/HavacHls.hpp:19)
 constexpr long long HALO_RESIDENT = 1ll << 24;       // symbols kept left of a shard (>= MAX_ROWS - 1)
 
-enum KernelKind { KERNEL_AUTO = 0, KERNEL_F16X2 = 1, KERNEL_SCALAR = 2 };
+enum KernelKind { KERNEL_AUTO = 0, KERNEL_F16X2 = 1, KERNEL_SCALAR = 2, KERNEL_F16X2_STREAMING = 3 };
 
 struct DeviceResultBlock {
   unsigned long long hitCount;  // total hits found (may exceed the capacity -> overflow)

@@ -119,10 +119,12 @@ int launch_all(havac_cuda_client* c) {
       p.smCycles = d.dCycles;
       d.lastLoadBegin = loadBegin;
       d.lastDiagBegin = p.diagBegin;
-      d.lastTiles = p.nTiles;
-      d.lastTileDiags = SSV_TILE_DIAGS;
+      const bool streamingOnly = c->kernel == KERNEL_F16X2_STREAMING;
+      const bool warpTiles = c->kernel != KERNEL_SCALAR && ssv_takes_short_kernel(p.nRows, streamingOnly);
+      d.lastTiles = warpTiles ? p.nTiles * (SSV_TILE_DIAGS / SSV_WARP_TILE_DIAGS) : p.nTiles;
+      d.lastTileDiags = warpTiles ? SSV_WARP_TILE_DIAGS : SSV_TILE_DIAGS;
       if (c->kernel == KERNEL_SCALAR) ssv_launch_scalar(p, d.stream);
-      else ssv_launch_f16x2(p, d.numSMs, d.stream);
+      else ssv_launch_f16x2(p, d.numSMs, d.stream, streamingOnly);
       CK(cudaGetLastError());
       c->launches++;
     }
@@ -707,6 +709,7 @@ int havac_cuda_set_kernel(havac_cuda_client* c, const char* name) {
   if (s == "auto") c->kernel = KERNEL_AUTO;
   else if (s == "f16x2") c->kernel = KERNEL_F16X2;
   else if (s == "scalar") c->kernel = KERNEL_SCALAR;
+  else if (s == "f16x2-streaming") c->kernel = KERNEL_F16X2_STREAMING;
   else return fail(c, HAVAC_CUDA_E_INVALID, "unknown kernel '" + s + "'");
   return HAVAC_CUDA_OK;
 }

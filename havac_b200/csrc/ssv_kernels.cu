@@ -37,6 +37,7 @@
 #include <cuda_runtime.h>
 #include <atomic>
 #include <cstdint>
+#include <cstdlib>
 
 #include "ssv_kernels.cuh"
 
@@ -296,11 +297,13 @@ __device__ __forceinline__ void cp_async16(void* dst, const void* src, uint32_t 
 // Write the 16 window entries of the symbols in packed word `x` (symbol offsets s .. s+15 from
 // the tile's first diagonal, s a multiple of 16); `xNext` is the following packed word, whose
 // first symbol completes the last window.
-__device__ __forceinline__ void ring_fill16(FastSmem& sm, uint32_t s, uint32_t x, uint32_t xNext) {
+// `ring` points at plane 0 of a ring of `nslot` 32-symbol groups per plane (the CTA-wide ring of the streaming
+// kernels, or one warp's private ring in the short-table kernel).
+__device__ __forceinline__ void ring_fill16(uint4* ring, uint32_t nslot, uint32_t s, uint32_t x, uint32_t xNext) {
   const uint4 o = expand16(x);
   const uint32_t o4 = 0x10u + 0x22u * (xNext & 3u);
   const uint32_t ow[5] = {o.x, o.y, o.z, o.w, o4};
-  const uint32_t slot = (s >> 5) % (uint32_t)NSLOT;
+  const uint32_t slot = (s >> 5) % nslot;
   const uint32_t plane0 = (s & 31u) >> 2;  // 0 or 4
 #pragma unroll
   for (int q = 0; q < 4; q++) {
@@ -309,16 +312,16 @@ __device__ __forceinline__ void ring_fill16(FastSmem& sm, uint32_t s, uint32_t x
     v.y = __funnelshift_r(ow[q], ow[q + 1], 8);
     v.z = __funnelshift_r(ow[q], ow[q + 1], 16);
     v.w = __funnelshift_r(ow[q], ow[q + 1], 24);
-    sm.ring[plane0 + q][slot] = v;
+    ring[(plane0 + q) * nslot + slot] = v;
   }
 }
 
 // The same for 64 symbols (one 128-bit vector of the packed sequence plus the word after it).
-__device__ __forceinline__ void ring_fill64(FastSmem& sm, uint32_t s, uint4 v, uint32_t next) {
-  ring_fill16(sm, s, v.x, v.y);
-  ring_fill16(sm, s + 16u, v.y, v.z);
-  ring_fill16(sm, s + 32u, v.z, v.w);
-  ring_fill16(sm, s + 48u, v.w, next);
+__device__ __forceinline__ void ring_fill64(uint4* ring, uint32_t nslot, uint32_t s, uint4 v, uint32_t next) {
+  ring_fill16(ring, nslot, s, v.x, v.y);
+  ring_fill16(ring, nslot, s + 16u, v.y, v.z);
+  ring_fill16(ring, nslot, s + 32u, v.z, v.w);
+  ring_fill16(ring, nslot, s + 48u, v.w, next);
 }
 
 // PRMT with the raw PTX semantics (CUDA's __byte_perm would first AND the selector with
@@ -389,13 +392,21 @@ __device__ __noinline__ uint32_t on_hit(const SsvParams& prm, uint32_t v, long l
   return v;
 }
 
-__device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, FastSmem& sm, const uint2* tab, uint32_t infMask, bool edge,
+struct ReplayGeom {
+  uint32_t ckBase;    // shared address of ckpt[0][0] (the thread's slots are found from threadIdx.x)
+  uint32_t ringBase;  // shared address of plane 0 of the ring the thread's windows live in
+  uint32_t nslot;     // 32-symbol groups per plane of that ring
+  uint32_t tabBase;   // shared address of the table row with index (row & tabMask) == 0
+  uint32_t tabMask;   // rows of the staged table chunk - 1
+};
+
+__device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, const ReplayGeom geo, uint32_t infMask, bool edge,
                                             long long d0, long long D0, uint32_t pb, uint32_t nRowsReplay) {
   // Registers do not cross this call: the caller says which of its registers hold an inf
   // (infMask), the exact end state of every replayed register is written over its checkpoint
   // slot, and the returned mask tells the caller which slots to read back. Shared memory is read
   // with shared-space addresses (a generic pointer would cost an address translation per load).
-  const uint32_t ckBase = smem_u32(&sm.ckpt[0][0]), ringBase = smem_u32(&sm.ring[0][0]), tabBase = smem_u32(tab);
+  const uint32_t ckBase = geo.ckBase, ringBase = geo.ringBase, tabBase = geo.tabBase, NSL = geo.nslot;
   uint32_t changed = 0;
 #pragma unroll 1
   for (uint32_t todo = edge ? 0xffffu : infMask; todo; todo &= todo - 1) {
@@ -419,8 +430,8 @@ __device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, FastSmem& sm, 
 #pragma unroll 1
       for (uint32_t r = 0; r < nRowsReplay; r++) {
         const uint32_t sy = s0 + r, p = pb + r;
-        const uint32_t sel = lds_u32(ringBase + (((sy & 31u) >> 2) * (uint32_t)NSLOT + (sy >> 5) % (uint32_t)NSLOT) * 16u + (sy & 3u) * 4u);
-        const uint2 e2 = lds_v2(tabBase + (p & (TC - 1)) * 8u);
+        const uint32_t sel = lds_u32(ringBase + (((sy & 31u) >> 2) * NSL + (sy >> 5) % NSL) * 16u + (sy & 3u) * 4u);
+        const uint2 e2 = lds_v2(tabBase + (p & geo.tabMask) * 8u);
         v = hfma2_relu_add(prmt(e2.x, e2.y, sel), v);
         const long long j = dlo + (long long)p;
         if (j < 0) v &= 0xffff0000u;
@@ -435,14 +446,14 @@ __device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, FastSmem& sm, 
 #pragma unroll 1
       for (uint32_t rb = 0; rb < nRowsReplay; rb += 16) {
         const uint32_t sA = s0 + rb, qA = sA >> 5;
-        const uint32_t slotA = qA % (uint32_t)NSLOT, slotB = slotA + 1 == (uint32_t)NSLOT ? 0u : slotA + 1;
+        const uint32_t slotA = qA % NSL, slotB = slotA + 1 == NSL ? 0u : slotA + 1;
         uint32_t m[16];
 #pragma unroll
         for (uint32_t i = 0; i < 16; i++) {
           const uint32_t sy = sA + i;
           const uint32_t sl = (sy >> 5) == qA ? slotA : slotB;
-          const uint32_t sel = lds_u32(ringBase + (((sy & 31u) >> 2) * (uint32_t)NSLOT + sl) * 16u + (sy & 3u) * 4u);
-          const uint2 e2 = lds_v2(tabBase + ((pb + rb + i) & (TC - 1)) * 8u);
+          const uint32_t sel = lds_u32(ringBase + (((sy & 31u) >> 2) * NSL + sl) * 16u + (sy & 3u) * 4u);
+          const uint2 e2 = lds_v2(tabBase + ((pb + rb + i) & geo.tabMask) * 8u);
           m[i] = prmt(e2.x, e2.y, sel);
         }
         uint32_t vv = v;
@@ -470,7 +481,8 @@ __device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, FastSmem& sm, 
 //   rows 4U+0..3 -> (q, c) = (2U,0) (2U,1) (2U+1,0) (2U+1,1)
 //   register k at row r needs the window of symbol d0 + 2k + r: even rows read e0, odd rows e1,
 //   and the slot a row just finished with is refilled with the window 32 symbols further on.
-template <int U>
+// NS = 32-symbol groups per plane of the ring the windows come from (compile time: it is an address stride)
+template <int U, int NS>
 __device__ __forceinline__ void four_rows(uint32_t (&w)[R], uint32_t (&e0)[R], uint32_t (&e1)[R],
                                           const uint2* __restrict__ tabRow,
                                           const uint4* __restrict__ ringSlot) {
@@ -478,7 +490,7 @@ __device__ __forceinline__ void four_rows(uint32_t (&w)[R], uint32_t (&e0)[R], u
   // die in rows 4U and 4U+1 (resp. 4U+2 and 4U+3) two rows before its first use, which is what lets the block
   // scheduler (havac_b200/sass/reblock.py) keep every window in one register for the whole block.
   // (ld.volatile: ptxas fuses two adjacent plain 64-bit loads, inline asm or not, back into one LDS.128.)
-  const uint32_t ringAddr = smem_u32(ringSlot + U * NSLOT);
+  const uint32_t ringAddr = smem_u32(ringSlot + U * NS);
   uint2 win01, win23;  // windows of the next block: rows 4U, 4U+1 and rows 4U+2, 4U+3
   asm volatile("ld.volatile.shared.v2.u32 {%0, %1}, [%2];" : "=r"(win01.x), "=r"(win01.y) : "r"(ringAddr));
   asm volatile("ld.volatile.shared.v2.u32 {%0, %1}, [%2+8];" : "=r"(win23.x), "=r"(win23.y) : "r"(ringAddr));
@@ -499,16 +511,16 @@ __device__ __forceinline__ void four_rows(uint32_t (&w)[R], uint32_t (&e0)[R], u
   e1[Q1 % R] = win23.y;
 }
 
-template <int U>
+template <int U, int NS>
 struct RowGroups {
   static __device__ __forceinline__ void run(uint32_t (&w)[R], uint32_t (&e0)[R], uint32_t (&e1)[R],
                                              const uint2* tabRow, const uint4* ringSlot) {
-    four_rows<U>(w, e0, e1, tabRow, ringSlot);
-    RowGroups<U + 1>::run(w, e0, e1, tabRow, ringSlot);
+    four_rows<U, NS>(w, e0, e1, tabRow, ringSlot);
+    RowGroups<U + 1, NS>::run(w, e0, e1, tabRow, ringSlot);
   }
 };
-template <>
-struct RowGroups<BLOCK_ROWS / 4> {
+template <int NS>
+struct RowGroups<BLOCK_ROWS / 4, NS> {
   static __device__ __forceinline__ void run(uint32_t (&)[R], uint32_t (&)[R], uint32_t (&)[R],
                                              const uint2*, const uint4*) {}
 };
@@ -516,16 +528,16 @@ struct RowGroups<BLOCK_ROWS / 4> {
 // The first END groups of a block only: the last block of a tile's rows when the table does not
 // end on a 32-row boundary (a 200-row model would otherwise pay for 224 rows). Nothing runs after
 // it in the tile, so the window registers it leaves half rotated are never used again.
-template <int U, int END>
+template <int U, int END, int NS>
 struct RowGroupsTo {
   static __device__ __forceinline__ void run(uint32_t (&w)[R], uint32_t (&e0)[R], uint32_t (&e1)[R],
                                              const uint2* tabRow, const uint4* ringSlot) {
-    four_rows<U>(w, e0, e1, tabRow, ringSlot);
-    RowGroupsTo<U + 1, END>::run(w, e0, e1, tabRow, ringSlot);
+    four_rows<U, NS>(w, e0, e1, tabRow, ringSlot);
+    RowGroupsTo<U + 1, END, NS>::run(w, e0, e1, tabRow, ringSlot);
   }
 };
-template <int END>
-struct RowGroupsTo<END, END> {
+template <int END, int NS>
+struct RowGroupsTo<END, END, NS> {
   static __device__ __forceinline__ void run(uint32_t (&)[R], uint32_t (&)[R], uint32_t (&)[R],
                                              const uint2*, const uint4*) {}
 };
@@ -593,7 +605,7 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
       long long need = (long long)W + ((rowEnd - (long long)p0 + 63) & ~63ll) + 64;
       if (need > W + 2 * TC) need = W + 2 * TC;
       for (int i = tid; i < (int)(need / 64); i += THREADS)
-        ring_fill64(sm, p0 + 64u * (uint32_t)i, load_seq_vec(prm, wFill0 + 4 * i), load_seq_word(prm, wFill0 + 4 * i + 4));
+        ring_fill64(&sm.ring[0][0], NSLOT, p0 + 64u * (uint32_t)i, load_seq_vec(prm, wFill0 + 4 * i), load_seq_word(prm, wFill0 + 4 * i + 4));
     }
     __syncthreads();
     aborted = sm.abortSeen[2] != 0;  // CTA-uniform: written before the barrier above
@@ -646,12 +658,12 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
 #endif
         if constexpr (TAIL) {
           const uint32_t left = pbEnd - pb;  // rows of the tile from this block on
-          if (left > 24) RowGroups<0>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
-          else if (left > 16) RowGroupsTo<0, 6>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
-          else if (left > 8) RowGroupsTo<0, 4>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
-          else RowGroupsTo<0, 2>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
+          if (left > 24) RowGroups<0, NSLOT>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
+          else if (left > 16) RowGroupsTo<0, 6, NSLOT>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
+          else if (left > 8) RowGroupsTo<0, 4, NSLOT>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
+          else RowGroupsTo<0, 2, NSLOT>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
         } else {
-          RowGroups<0>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
+          RowGroups<0, NSLOT>::run(w, e0, e1, tabRow, &sm.ring[0][g]);
         }
         tabRow += BLOCK_ROWS;
         g = (g + 1 == (uint32_t)NSLOT) ? 0u : g + 1;
@@ -669,7 +681,8 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
           uint32_t infMask = 0;
 #pragma unroll
           for (int k = 0; k < R; k++) infMask |= has_inf(w[k]) ? (1u << k) : 0u;
-          const uint32_t changed = exact_rows(prm, sm, sm.tab[buf], infMask, edge, d0, D0, pb, BLOCK_ROWS);
+          const ReplayGeom geo{smem_u32(&sm.ckpt[0][0]), smem_u32(&sm.ring[0][0]), (uint32_t)NSLOT, smem_u32(sm.tab[buf]), (uint32_t)TC - 1u};
+          const uint32_t changed = exact_rows(prm, geo, infMask, edge, d0, D0, pb, BLOCK_ROWS);
           const uint32_t* ck = reinterpret_cast<const uint32_t*>(&sm.ckpt[0][0]);
 #pragma unroll
           for (int k = 0; k < R; k++)
@@ -692,12 +705,124 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
         break;
       }
       if (doRefill && tid < TC / 64)
-        ring_fill64(sm, sRefill + 64u * (uint32_t)tid, sm.seqStage[buf][tid], sm.seqStage[buf][tid + 1].x);
+        ring_fill64(&sm.ring[0][0], NSLOT, sRefill + 64u * (uint32_t)tid, sm.seqStage[buf][tid], sm.seqStage[buf][tid + 1].x);
     }
     __syncthreads();
     if (aborted) break;
   }
   if (tid == 0 && aborted) atomicOr(prm.status, SSV_STATUS_ABORTED);
+  if (tid == 0 && blockIdx.x == 0) *prm.smCycles = (unsigned long long)(clock64() - clk0);
+}
+
+// =======================================================================================
+// Short tables (at most SHORT_ROWS rows): every WARP is on its own
+// =======================================================================================
+// A streaming tile costs two CTA-wide barriers and a dependent chain global load -> window expansion -> barrier ->
+// window loads before its first block, whatever the number of rows: at 72 rows the warps of the streaming kernel
+// spend 22 % of their time at those barriers and another 9 % waiting for the loads (profiles/r2_ncu_rows72.txt).
+// A table of at most 512 rows fits in shared memory whole (4 KB), so nothing has to be streamed and nothing
+// has to be shared between warps but that table: here a warp takes 1024 diagonals of its own from the tile counter,
+// fills a PRIVATE ring of selector windows (1024 + rows + 64 symbols), runs the same 32-row blocks over all rows and
+// fetches the next 1024 diagonals -- no barrier after the table has been loaded, so the warps of an SM drift apart
+// and one warp's load latency is another warp's compute.
+constexpr int SHORT_ROWS = SSV_SHORT_ROWS;                 // rows the short-table kernel accepts (multiple of 32)
+constexpr int WARP_DIAGS = 32 * 2 * R;                     // 1024 diagonals per warp tile
+constexpr int NS_SHORT = (WARP_DIAGS + SHORT_ROWS + 64) / 32;  // 32-symbol groups per plane of a warp's ring (never wraps)
+constexpr int WARPS = THREADS / 32;
+
+struct __align__(16) ShortSmem {
+  uint4 ring[WARPS][8][NS_SHORT];
+  uint2 tab[SHORT_ROWS];
+  uint4 ckpt[R / 4][THREADS];
+};
+
+__global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_short_kernel(const SsvParams prm) {
+  extern __shared__ __align__(16) unsigned char smemRaw[];
+  ShortSmem& sm = *reinterpret_cast<ShortSmem*>(smemRaw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long long clk0 = clock64();
+  // the whole table, once per CTA (pad rows of the device table are -128: they can never hit)
+  const uint32_t rowsPad = (prm.nRows + BLOCK_ROWS - 1) / BLOCK_ROWS * BLOCK_ROWS;
+  for (uint32_t r = tid; r < rowsPad; r += THREADS) sm.tab[r] = __ldg(prm.tab16 + r);
+  __syncthreads();
+
+  uint4* ring = &sm.ring[warp][0][0];
+  const uint32_t nTilesW = prm.nTiles * (uint32_t)(W / WARP_DIAGS);
+  bool aborted = false;
+  while (true) {
+    unsigned ticket = 0;
+    int stop = 0;
+    if (lane == 0) {
+      ticket = atomicAdd(prm.tileCounter, 1u);
+      stop = *prm.abortFlag;
+    }
+    ticket = __shfl_sync(FULL, ticket, 0);
+    aborted = __shfl_sync(FULL, stop, 0) != 0;
+    if (ticket >= nTilesW || aborted) break;
+    const unsigned tile = nTilesW - 1u - ticket;  // right to left, as in the streaming kernels
+    const long long D0 = prm.diagBegin + (long long)tile * WARP_DIAGS;
+    const long long d0 = D0 + (long long)lane * (2 * R);
+    long long rowEnd = prm.nLoad - D0;
+    if (rowEnd > (long long)prm.nRows) rowEnd = prm.nRows;
+    if (rowEnd <= 0 || D0 + WARP_DIAGS - 1 + (long long)prm.nRows - 1 < 0) continue;  // nothing real in this band
+    const uint32_t edgeRows = D0 < 0 ? (uint32_t)(-D0 < 0x7fffffffll ? -D0 : 0x7fffffffll) : 0u;
+    const uint32_t pbEnd = (uint32_t)rowEnd;
+
+    // ring: the windows of symbols [D0, D0 + 1024 + rows + 64), 64 per lane and pass
+    {
+      const long long wFill0 = D0 >> 4;  // D0 is a multiple of 64
+      const int n64 = (WARP_DIAGS + (int)((pbEnd + 63u) & ~63u) + 64) / 64;
+      for (int i = lane; i < n64; i += 32)
+        ring_fill64(ring, NS_SHORT, 64u * (uint32_t)i, load_seq_vec(prm, wFill0 + 4 * i), load_seq_word(prm, wFill0 + 4 * i + 4));
+    }
+    __syncwarp();
+
+    uint32_t w[R], e0[R], e1[R];
+    uint32_t g = (uint32_t)lane;  // slot of symbol offset 32 lane
+#pragma unroll
+    for (int u = 0; u < R / 2; u++) {
+      const uint4 v = ring[u * NS_SHORT + g];
+      e0[2 * u] = v.x;
+      e1[2 * u] = v.y;
+      e0[2 * u + 1] = v.z;
+      e1[2 * u + 1] = v.w;
+    }
+#pragma unroll
+    for (int k = 0; k < R; k++) w[k] = 0u;
+    g += 1;
+
+    const uint2* tabRow = sm.tab;
+    for (uint32_t pb = 0; pb < pbEnd; pb += BLOCK_ROWS) {
+#pragma unroll
+      for (int q = 0; q < R / 4; q++)
+        sm.ckpt[q][tid] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+      const uint32_t left = pbEnd - pb;  // rows of the tile from this block on
+      if (left > 24) RowGroups<0, NS_SHORT>::run(w, e0, e1, tabRow, ring + g);
+      else if (left > 16) RowGroupsTo<0, 6, NS_SHORT>::run(w, e0, e1, tabRow, ring + g);
+      else if (left > 8) RowGroupsTo<0, 4, NS_SHORT>::run(w, e0, e1, tabRow, ring + g);
+      else RowGroupsTo<0, 2, NS_SHORT>::run(w, e0, e1, tabRow, ring + g);
+      tabRow += BLOCK_ROWS;
+      g += 1;  // 32 + rows / 32 + 1 groups at most: the private ring never wraps
+
+      uint32_t mx = 0;
+#pragma unroll
+      for (int k = 0; k < R; k += 2) mx = __vimax3_s16x2(mx, w[k], w[k + 1]);
+      const bool edge = pb < edgeRows;
+      if (edge || __any_sync(FULL, has_inf(mx))) {
+        uint32_t infMask = 0;
+#pragma unroll
+        for (int k = 0; k < R; k++) infMask |= has_inf(w[k]) ? (1u << k) : 0u;
+        const ReplayGeom geo{smem_u32(&sm.ckpt[0][0]), smem_u32(ring), (uint32_t)NS_SHORT, smem_u32(sm.tab), 0xffffffffu};
+        const uint32_t changed = exact_rows(prm, geo, infMask, edge, d0, D0, pb, BLOCK_ROWS);
+        const uint32_t* ck = reinterpret_cast<const uint32_t*>(&sm.ckpt[0][0]);
+#pragma unroll
+        for (int k = 0; k < R; k++)
+          if ((changed >> k) & 1u) w[k] = ck[((k >> 2) * THREADS + tid) * 4 + (k & 3)];
+      }
+    }
+    __syncwarp();  // every lane has read its last windows before the ring is refilled
+  }
+  if (lane == 0 && aborted) atomicOr(prm.status, SSV_STATUS_ABORTED);
   if (tid == 0 && blockIdx.x == 0) *prm.smCycles = (unsigned long long)(clock64() - clk0);
 }
 
@@ -778,6 +903,9 @@ int ssv_f16x2_ctas_per_sm() {
     if (have > 0) return have;
   }
   cudaError_t e = cudaSuccess;
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(ssv_f16x2_short_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShortSmem));
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(ssv_f16x2_short_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   for (auto kernel : {ssv_f16x2_kernel, ssv_f16x2_tail_kernel}) {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem));
     if (e == cudaSuccess)
@@ -790,8 +918,18 @@ int ssv_f16x2_ctas_per_sm() {
   return n;
 }
 
-void ssv_launch_f16x2(const SsvParams& prm, int numSMs, void* stream) {
+bool ssv_takes_short_kernel(uint32_t nRows, bool streamingOnly) { return nRows <= (uint32_t)SHORT_ROWS && !streamingOnly; }
+
+void ssv_launch_f16x2(const SsvParams& prm, int numSMs, void* stream, bool streamingOnly) {
   int grid = numSMs * ssv_f16x2_ctas_per_sm();
+  if (ssv_takes_short_kernel(prm.nRows, streamingOnly)) {
+    // whole table in shared memory, warps on their own (the grid never exceeds the 8192-diagonal tiles there are,
+    // each of which is eight warp tiles)
+    if ((unsigned)grid > prm.nTiles) grid = (int)prm.nTiles;
+    if (grid < 1) grid = 1;
+    ssv_f16x2_short_kernel<<<grid, THREADS, sizeof(ShortSmem), (cudaStream_t)stream>>>(prm);
+    return;
+  }
   if ((unsigned)grid > prm.nTiles) grid = (int)prm.nTiles;
   if (grid < 1) grid = 1;
   // A table that ends 1..24 rows into its last 32-row block can skip the 8, 16 or 24 rows it does not

@@ -57,13 +57,21 @@ constexpr int SSV_TILE_DIAGS = SSV_THREADS * 2 * SSV_R;  // 8192
 #endif
 constexpr int SSV_ROW_CHUNK = SSV_ROW_CHUNK_V;   // rows of the score table staged per TMA bulk copy
 constexpr int SSV_BLOCK_ROWS = 2 * SSV_R;
+#ifndef SSV_SHORT_ROWS_V
+#define SSV_SHORT_ROWS_V 512
+#endif
+constexpr int SSV_SHORT_ROWS = SSV_SHORT_ROWS_V;  // tables up to this many rows take the short-table kernel (warps on their own)
+constexpr int SSV_WARP_TILE_DIAGS = 32 * 2 * SSV_R;  // diagonals of a warp tile there
 
 // host-callable launchers (defined in ssv_kernels.cu); all asynchronous on `stream`.
 void ssv_launch_table_prep(const int8_t* tab8, uint32_t nRows, uint2* tab16, uint32_t rowsPadded,
                            void* stream);
 void ssv_launch_project_table(const float* emissions, uint32_t nRows, const uint32_t* modelFirstRow, const float* alphaBeta,
                               uint32_t nModels, int8_t* tab8, void* stream);
-void ssv_launch_f16x2(const SsvParams& prm, int numSMs, void* stream);
+// streamingOnly: tables short enough for the short-table kernel take the streaming kernels all the same (parity tests
+// of the streaming kernels' partial last block, A/B measurements)
+void ssv_launch_f16x2(const SsvParams& prm, int numSMs, void* stream, bool streamingOnly = false);
+bool ssv_takes_short_kernel(uint32_t nRows, bool streamingOnly);
 void ssv_launch_scalar(const SsvParams& prm, void* stream);
 void ssv_launch_trace(const SsvParams& prm, uint32_t rowBegin, uint32_t rowEnd, long long colBegin, long long colEnd,
                       SsvCellRecord* out, void* stream);

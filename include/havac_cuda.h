@@ -202,8 +202,9 @@ int havac_cuda_cell_selftest(havac_cuda_client* c, uint8_t* score, uint8_t* hit)
  * it to aim their diagonal replays at tile / thread / chunk / block edges. Any pointer may be NULL. */
 int havac_cuda_tile_geometry(havac_cuda_client* c, uint32_t device, int64_t* loadBegin, int64_t* diagBegin, uint32_t* nTiles,
                              uint32_t* tileDiagonals, uint32_t* rowChunk, uint32_t* blockRows);
-/* Select a kernel variant by name ("auto" | "f16x2" | "scalar"); for tests that
- * cross-check the fast path against the plain one. */
+/* Select a kernel variant by name ("auto" | "f16x2" | "f16x2-streaming" | "scalar"); for tests that cross-check the
+ * fast path against the plain one. "f16x2-streaming" keeps tables of at most 512 rows away from the short-table
+ * kernel (every warp on its own) so that the streaming kernels can be tested with short tables too. */
 int havac_cuda_set_kernel(havac_cuda_client* c, const char* name);
 
 #ifdef __cplusplus

@@ -59,7 +59,7 @@ def oracle_hits(packed, table):
     return np.sort(O.encode_hits(pos, row))
 
 
-def check(packed, table, kernels=("f16x2", "scalar"), min_hits=1):
+def check(packed, table, kernels=("f16x2", "f16x2-streaming", "scalar"), min_hits=1):
     want = oracle_hits(packed, table)
     assert len(want) >= min_hits, "test input produced too few oracle hits to be meaningful"
     for k in kernels:
@@ -177,8 +177,9 @@ def test_every_tail_length():
         t[-1, :] = 60  # whatever a diagonal holds above 195 hits in the last row
         want = oracle_hits(packed, t)
         assert (want >> np.uint64(40)).max() == rows - 1, "no hit in the last row: the case would prove nothing"
-        got = np.sort(gpu_hits(packed, t, "f16x2"))
-        assert np.array_equal(got, want), f"rows={rows}: {len(got)} hits vs oracle {len(want)}"
+        for kernel in ("f16x2", "f16x2-streaming"):  # the short-table kernel (warps on their own) and the streaming kernel's tail build
+            got = np.sort(gpu_hits(packed, t, kernel))
+            assert np.array_equal(got, want), f"rows={rows} {kernel}: {len(got)} hits vs oracle {len(want)}"
 
 
 def test_cell_update_exhaustive():
@@ -210,3 +211,45 @@ def test_cell_update_exhaustive():
     for half in (0, 1):
         assert np.array_equal(hit[half] & 1, want_hit), f"hit flags differ in fp16 half {half}"
         assert np.array_equal(score[half], want_score), f"scores differ in fp16 half {half}"
+
+
+def test_short_table_kernel_edges():
+    """Tables of at most 512 rows take the short-table kernel: 1024 diagonals per WARP, a private selector ring per warp,
+    no barrier between tiles. Row counts around its limits (1, 31, 32, 33, 511, 512; 513 is the streaming kernel's), a
+    sequence of exactly one segment and of many, hit-dense so that every warp tile replays, against the oracle; and the
+    planted-hit technique of the full-size test at the edges of WARP tiles (diagonal 0, 1, 31, 32, 1022, 1023 of a tile)."""
+    g = synth.rng(12, 1)
+    full = g.integers(-20, 60, size=(520, 4)).astype(np.int8)
+    for n_seg, row_counts in ((1, (1, 31, 32, 33, 512)), (5, (2, 64, 100, 511, 512, 513))):
+        packed = synth.pack_2bit(synth.random_symbols(12 + n_seg, n_seg * 12_288 - 3))
+        for rows in row_counts:
+            t = np.ascontiguousarray(full[:rows])
+            want = oracle_hits(packed, t)
+            got = np.sort(gpu_hits(packed, t, "f16x2"))
+            assert np.array_equal(got, want), f"rows={rows}, {n_seg} segments: {len(got)} hits vs oracle {len(want)}"
+    # sparse table, hits planted on warp-tile edges
+    table, cons = consensus_table(13, 480)
+    n = 40 * 12_288
+    packed = synth.pack_2bit(planted_sequence(13, n, cons, 20))
+    c = HavacHwClient("")
+    try:
+        c.writeSequence(packed)
+        c.writePhmm(table)
+        c.invokeHavacSsvAsync()
+        assert c.waitForHavacSsvAsync() == STATE_COMPLETED
+        geom = c.tileGeometry()
+        assert geom["tileDiagonals"] == 1024
+        gg = np.random.Generator(np.random.PCG64(5))
+        planted = [(d, r) for d, r in O.edge_targets(geom, 480, n, seed=3, n_tiles=6) if O.plant_hit_at(packed, table, d, r, gg) is not None]
+        assert len(planted) >= 12
+        c.writeSequence(packed)
+        c.invokeHavacSsvAsync()
+        assert c.waitForHavacSsvAsync() == STATE_COMPLETED
+        got = np.sort(c.getHitList())
+    finally:
+        c.close()
+    want = oracle_hits(packed, table)
+    assert np.array_equal(got, want)
+    have = set(got.tolist())
+    for d, r in planted:
+        assert int(O.encode_hits([d + r], [r])[0]) in have

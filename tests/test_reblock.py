@@ -30,7 +30,7 @@ def shipped():
     if not os.path.exists(build.CUDA_LIB):
         build.build_cuda()
     ks = fast_kernels(build.CUDA_LIB)
-    assert len(ks) == 2, "plain and tail build of the fast kernel"
+    assert len(ks) == 3, "the streaming kernel, its tail build, and the short-table kernel"
     return ks
 
 
@@ -57,11 +57,11 @@ def test_shipped_blocks_are_the_re_emitted_ones(shipped):
             # every lookup / update issues with a stall count of 1 except the pipeline's ends
             slow = [x for x in P + H if R.get_ctl(x.w1)["stall"] != 1]
             assert len(slow) <= 2 * R.LAG + 2
-    assert n_blocks == 5, "one block in the plain kernel, four row counts in the tail kernel"
+    assert n_blocks == 9, "one block in the streaming kernel, four row counts each in its tail build and in the short-table kernel"
 
 
 def _block_of_plain_kernel(shipped):
-    name = next(n for n in shipped if "tail" not in n)
+    name = next(n for n in shipped if "tail" not in n and "short" not in n)
     blk = R.find_blocks(shipped[name])[0]
     for i, x in enumerate(blk):
         x.uid = i
@@ -99,7 +99,7 @@ def test_re_running_the_tool_on_its_own_output_proves_it_again(shipped, tmp_path
         pytest.skip("no kept cubin (library was built elsewhere)")
     out = str(tmp_path / "again.cubin")
     report = R.patch_cubin(cubin, out, verbose=False)
-    assert len(report) == 2
+    assert len(report) == 3
     for name, blocks in report.items():
         assert blocks and all(b[2] == "rescheduled" for b in blocks), (name, blocks)
     a = fast_kernels(cubin)
@@ -117,4 +117,4 @@ def test_fresh_compile_is_fully_rescheduled(tmp_path):
     subprocess.run([nvcc, *build.NVCC_FLAGS, "-cubin", "-I", build.INCLUDE, "-o", cubin, os.path.join(build.CSRC, "ssv_kernels.cu")], check=True)
     report = R.patch_cubin(cubin, str(tmp_path / "patched.cubin"), verbose=False)
     rows = sorted(b[1] for blocks in report.values() for b in blocks)
-    assert rows == [8, 16, 24, 32, 32], report
+    assert rows == [8, 8, 16, 16, 24, 24, 32, 32, 32], report

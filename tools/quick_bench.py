@@ -18,6 +18,8 @@ def main():
     t[np.arange(rows), g.integers(0, 4, size=rows)] = g.integers(pos_lo, pos_lo + 9, size=rows)
     packed = synth.random_packed(99, n)
     c = HavacHwClient(";hitcap=200000000+")
+    if os.environ.get("HAVAC_KERNEL"):
+        c.setKernel(os.environ["HAVAC_KERNEL"])
     c.writeSequence(packed); c.writePhmm(t)
     for i in range(reps):
         t0 = time.time(); c.invokeHavacSsvAsync(); st = c.waitForHavacSsvAsync(); wall = time.time() - t0
