@@ -228,6 +228,18 @@ struct __align__(16) FastSmem {
   int abortSeen[3];
 };
 
+// geometry of the short-table kernel (its description is at the kernel)
+constexpr int SHORT_ROWS = SSV_SHORT_ROWS;                 // rows the short-table kernel accepts (multiple of 32)
+constexpr int WARP_DIAGS = 32 * 2 * R;                     // 1024 diagonals per warp tile
+constexpr int NS_SHORT = (WARP_DIAGS + SHORT_ROWS + 64) / 32;  // 32-symbol groups per plane of a warp's ring (never wraps)
+constexpr int WARPS = THREADS / 32;
+
+struct __align__(16) ShortSmem {
+  uint4 ring[WARPS][8][NS_SHORT];
+  uint2 tab[SHORT_ROWS];
+  uint4 ckpt[R / 4][THREADS];
+};
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
 }
@@ -262,19 +274,6 @@ __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t
       : "memory");
 }
 
-// 16 packed symbols -> 16 selector bytes. Byte for symbol x: low nibble 2x, high nibble 2x+1,
-// i.e. "take bytes 2x and 2x+1 of the 8-byte score row" when used as a PRMT selector.
-__device__ __forceinline__ uint4 expand16(uint32_t x) {
-  uint32_t o[4];
-#pragma unroll
-  for (int i = 0; i < 4; i++) {
-    uint32_t b = (x >> (8 * i)) & 0xffu;
-    uint32_t s = (b & 3u) | ((b & 0xcu) << 6) | ((b & 0x30u) << 12) | ((b & 0xc0u) << 18);
-    o[i] = 0x10101010u + 0x22u * s;
-  }
-  return make_uint4(o[0], o[1], o[2], o[3]);
-}
-
 // Packed word holding local symbols [16*wi, 16*wi+16); zero ('A') outside the loaded range.
 __device__ __forceinline__ uint32_t load_seq_word(const SsvParams& prm, long long wi) {
   long long nWords = prm.nLoad >> 4;
@@ -294,26 +293,46 @@ __device__ __forceinline__ void cp_async16(void* dst, const void* src, uint32_t 
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(srcBytes) : "memory");
 }
 
+// PRMT with the raw PTX semantics (CUDA's __byte_perm would first AND the selector with
+// 0x7777). Only selector bits [15:0] are read; our nibbles are all <= 7 (plain byte copy).
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+  return r;
+}
+
 // Write the 16 window entries of the symbols in packed word `x` (symbol offsets s .. s+15 from
 // the tile's first diagonal, s a multiple of 16); `xNext` is the following packed word, whose
 // first symbol completes the last window.
+// The selector byte of symbol value v is byte v of 0x76543210, so PRMT does the expansion itself: with the packed
+// word masked to 0x3333 its selector nibbles ARE the even symbols (and shifted right by two, the odd ones): four
+// PRMTs turn 16 symbols into their selector bytes, even and odd positions apart, and one more PRMT per window puts
+// two neighbours side by side. Only bits [15:0] of a window are ever read (by the lookups' PRMT and by the
+// replay); the upper half holds whatever the same PRMT brings along.
 // `ring` points at plane 0 of a ring of `nslot` 32-symbol groups per plane (the CTA-wide ring of the streaming
 // kernels, or one warp's private ring in the short-table kernel).
 __device__ __forceinline__ void ring_fill16(uint4* ring, uint32_t nslot, uint32_t s, uint32_t x, uint32_t xNext) {
-  const uint4 o = expand16(x);
-  const uint32_t o4 = 0x10u + 0x22u * (xNext & 3u);
-  const uint32_t ow[5] = {o.x, o.y, o.z, o.w, o4};
+  constexpr uint32_t K = 0x76543210u;
+  const uint32_t e0 = prmt(K, 0u, x & 0x3333u);           // selectors of symbols 0 2 4 6
+  const uint32_t o0 = prmt(K, 0u, (x >> 2) & 0x3333u);    //                      1 3 5 7
+  const uint32_t e1 = prmt(K, 0u, (x >> 16) & 0x3333u);   //                      8 10 12 14
+  const uint32_t o1 = prmt(K, 0u, (x >> 18) & 0x3333u);   //                      9 11 13 15
+  const uint32_t nx = prmt(K, 0u, xNext & 0x3u);          // first symbol of the next word (byte 0)
   const uint32_t slot = (s >> 5) % nslot;
   const uint32_t plane0 = (s & 31u) >> 2;  // 0 or 4
-#pragma unroll
-  for (int q = 0; q < 4; q++) {
-    uint4 v;
-    v.x = ow[q];
-    v.y = __funnelshift_r(ow[q], ow[q + 1], 8);
-    v.z = __funnelshift_r(ow[q], ow[q + 1], 16);
-    v.w = __funnelshift_r(ow[q], ow[q + 1], 24);
-    ring[(plane0 + q) * nslot + slot] = v;
-  }
+  uint4 v;
+  // windows of symbols 0..3: (e0.0 o0.0) (o0.0 e0.1) (e0.1 o0.1) (o0.1 e0.2)
+  v.x = prmt(e0, o0, 0x5140u); v.y = prmt(e0, o0, 0x2514u); v.z = prmt(e0, o0, 0x6251u); v.w = prmt(e0, o0, 0x3625u);
+  ring[(plane0 + 0) * nslot + slot] = v;
+  // 4..7: (e0.2 o0.2) (o0.2 e0.3) (e0.3 o0.3) (o0.3 e1.0)
+  v.x = prmt(e0, o0, 0x7362u); v.y = prmt(e0, o0, 0x7736u); v.z = prmt(e0, o0, 0x7773u); v.w = prmt(o0, e1, 0x4443u);
+  ring[(plane0 + 1) * nslot + slot] = v;
+  // 8..11
+  v.x = prmt(e1, o1, 0x5140u); v.y = prmt(e1, o1, 0x2514u); v.z = prmt(e1, o1, 0x6251u); v.w = prmt(e1, o1, 0x3625u);
+  ring[(plane0 + 2) * nslot + slot] = v;
+  // 12..15: the last window ends with the next word's first symbol
+  v.x = prmt(e1, o1, 0x7362u); v.y = prmt(e1, o1, 0x7736u); v.z = prmt(e1, o1, 0x7773u); v.w = prmt(o1, nx, 0x4443u);
+  ring[(plane0 + 3) * nslot + slot] = v;
 }
 
 // The same for 64 symbols (one 128-bit vector of the packed sequence plus the word after it).
@@ -322,14 +341,6 @@ __device__ __forceinline__ void ring_fill64(uint4* ring, uint32_t nslot, uint32_
   ring_fill16(ring, nslot, s + 16u, v.y, v.z);
   ring_fill16(ring, nslot, s + 32u, v.z, v.w);
   ring_fill16(ring, nslot, s + 48u, v.w, next);
-}
-
-// PRMT with the raw PTX semantics (CUDA's __byte_perm would first AND the selector with
-// 0x7777). Only selector bits [15:0] are read; our nibbles are all <= 7 (plain byte copy).
-__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
-  uint32_t r;
-  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
-  return r;
 }
 
 __device__ __forceinline__ uint32_t hfma2_relu_add(uint32_t m, uint32_t w) {
@@ -392,16 +403,21 @@ __device__ __noinline__ uint32_t on_hit(const SsvParams& prm, uint32_t v, long l
   return v;
 }
 
-struct ReplayGeom {
-  uint32_t ckBase;    // shared address of ckpt[0][0] (the thread's slots are found from threadIdx.x)
-  uint32_t ringBase;  // shared address of plane 0 of the ring the thread's windows live in
-  uint32_t nslot;     // 32-symbol groups per plane of that ring
-  uint32_t tabBase;   // shared address of the table row with index (row & tabMask) == 0
-  uint32_t tabMask;   // rows of the staged table chunk - 1
-};
-
-__device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, const ReplayGeom geo, uint32_t infMask, bool edge,
+// SHORT: called from the short-table kernel (the warp's private ring, the whole table at `tab`) or from the streaming
+// kernels (the CTA's ring, `tab` = the staged chunk). The shared-memory addresses are found from the kernel family's
+// layout in here, so that the call costs the hot loop's register allocation no more than its six arguments.
+extern __shared__ __align__(16) unsigned char smemRaw[];
+template <bool SHORT>
+__device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, const uint2* tab, uint32_t infMask, bool edge,
                                             long long d0, long long D0, uint32_t pb, uint32_t nRowsReplay) {
+  struct Geom { uint32_t ckBase, ringBase, nslot, tabBase, tabMask; } geo;
+  if constexpr (SHORT) {
+    ShortSmem& sm = *reinterpret_cast<ShortSmem*>(smemRaw);
+    geo = {smem_u32(&sm.ckpt[0][0]), smem_u32(&sm.ring[threadIdx.x >> 5][0][0]), (uint32_t)NS_SHORT, smem_u32(tab), 0xffffffffu};
+  } else {
+    FastSmem& sm = *reinterpret_cast<FastSmem*>(smemRaw);
+    geo = {smem_u32(&sm.ckpt[0][0]), smem_u32(&sm.ring[0][0]), (uint32_t)NSLOT, smem_u32(tab), (uint32_t)TC - 1u};
+  }
   // Registers do not cross this call: the caller says which of its registers hold an inf
   // (infMask), the exact end state of every replayed register is written over its checkpoint
   // slot, and the returned mask tells the caller which slots to read back. Shared memory is read
@@ -546,7 +562,6 @@ struct RowGroupsTo<END, END, NS> {
 // plain build keeps the hot loop exactly as it was measured (the branch cost 2 % at 35 k rows).
 template <bool TAIL>
 __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
-  extern __shared__ __align__(16) unsigned char smemRaw[];
   FastSmem& sm = *reinterpret_cast<FastSmem*>(smemRaw);
   const int tid = threadIdx.x;
   uint32_t mbarPhase = 0;  // bit b = parity to wait for on sm.mbar[b]
@@ -681,8 +696,7 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
           uint32_t infMask = 0;
 #pragma unroll
           for (int k = 0; k < R; k++) infMask |= has_inf(w[k]) ? (1u << k) : 0u;
-          const ReplayGeom geo{smem_u32(&sm.ckpt[0][0]), smem_u32(&sm.ring[0][0]), (uint32_t)NSLOT, smem_u32(sm.tab[buf]), (uint32_t)TC - 1u};
-          const uint32_t changed = exact_rows(prm, geo, infMask, edge, d0, D0, pb, BLOCK_ROWS);
+          const uint32_t changed = exact_rows<false>(prm, sm.tab[buf], infMask, edge, d0, D0, pb, BLOCK_ROWS);
           const uint32_t* ck = reinterpret_cast<const uint32_t*>(&sm.ckpt[0][0]);
 #pragma unroll
           for (int k = 0; k < R; k++)
@@ -725,19 +739,7 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
 // fills a PRIVATE ring of selector windows (1024 + rows + 64 symbols), runs the same 32-row blocks over all rows and
 // fetches the next 1024 diagonals -- no barrier after the table has been loaded, so the warps of an SM drift apart
 // and one warp's load latency is another warp's compute.
-constexpr int SHORT_ROWS = SSV_SHORT_ROWS;                 // rows the short-table kernel accepts (multiple of 32)
-constexpr int WARP_DIAGS = 32 * 2 * R;                     // 1024 diagonals per warp tile
-constexpr int NS_SHORT = (WARP_DIAGS + SHORT_ROWS + 64) / 32;  // 32-symbol groups per plane of a warp's ring (never wraps)
-constexpr int WARPS = THREADS / 32;
-
-struct __align__(16) ShortSmem {
-  uint4 ring[WARPS][8][NS_SHORT];
-  uint2 tab[SHORT_ROWS];
-  uint4 ckpt[R / 4][THREADS];
-};
-
 __global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_short_kernel(const SsvParams prm) {
-  extern __shared__ __align__(16) unsigned char smemRaw[];
   ShortSmem& sm = *reinterpret_cast<ShortSmem*>(smemRaw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const long long clk0 = clock64();
@@ -812,8 +814,7 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_short_kernel
         uint32_t infMask = 0;
 #pragma unroll
         for (int k = 0; k < R; k++) infMask |= has_inf(w[k]) ? (1u << k) : 0u;
-        const ReplayGeom geo{smem_u32(&sm.ckpt[0][0]), smem_u32(ring), (uint32_t)NS_SHORT, smem_u32(sm.tab), 0xffffffffu};
-        const uint32_t changed = exact_rows(prm, geo, infMask, edge, d0, D0, pb, BLOCK_ROWS);
+        const uint32_t changed = exact_rows<true>(prm, sm.tab, infMask, edge, d0, D0, pb, BLOCK_ROWS);
         const uint32_t* ck = reinterpret_cast<const uint32_t*>(&sm.ckpt[0][0]);
 #pragma unroll
         for (int k = 0; k < R; k++)
