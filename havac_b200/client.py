@@ -31,7 +31,7 @@ EXPORTS = [
     "havac_cuda_device_time_ms", "havac_cuda_device_count", "havac_cuda_run_stats", "havac_cuda_set_kernel", "havac_cuda_transfer_stats", "havac_cuda_sm_cycles",
     "havac_cuda_ingest_fasta", "havac_cuda_ingest_records", "havac_cuda_read_sequence", "havac_cuda_resolve_hits", "havac_cuda_project_phmm", "havac_cuda_read_phmm",
     "havac_cuda_reverse_complement", "havac_cuda_strand_state", "havac_cuda_tile_geometry", "havac_cuda_cell_selftest",
-    "havac_cuda_trace_cells", "havac_cuda_debug_poke_phmm",
+    "havac_cuda_trace_cells", "havac_cuda_debug_poke_phmm", "havac_cuda_sort_hits_static",
 ]
 
 # one cell of the per-cell trace (include/havac_cuda.h havac_cuda_cell_record; byCellComparator.hpp:23-31)
@@ -90,6 +90,7 @@ def load_library(path: Optional[str] = None) -> C.CDLL:
     L.havac_cuda_debug_poke_phmm.argtypes = [vp, u64, C.c_int8]
     L.havac_cuda_tile_geometry.argtypes = [vp, u32, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(u32), C.POINTER(u32),
                                            C.POINTER(u32), C.POINTER(u32)]
+    L.havac_cuda_sort_hits_static.argtypes = [u32, vp, u64, vp, vp]
     for name in EXPORTS:
         if name != "havac_cuda_last_error":
             getattr(L, name).restype = C.c_int

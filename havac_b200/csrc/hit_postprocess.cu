@@ -17,6 +17,7 @@
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include <vector>
 
 #include "client_internal.cuh"
@@ -301,5 +302,109 @@ extern "C" int havac_cuda_resolve_hits(havac_cuda_client* c, const uint64_t* seq
                    secs(t0, t1), secs(t1, t2), secs(t2, now()));
   }
   *nOut = kept;
+  return HAVAC_CUDA_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Emission-order sort with NO allocation (havac_cuda_sort_hits_static, include/havac_cuda.h). No counterpart in the
+// reference; added for callers that cannot call cudaMalloc (code under CUDA
+// graph capture, tight serving loops, harnesses that forbid it). The launch sequence is the one of
+// havac_sort_hits_on_device above, with every buffer that function takes from cudaMalloc laid out in ONE file-scope
+// device array instead. Every GPU that loads the library holds the array (16.25 MiB) until the process exits.
+//
+// Scratch layout (bytes), for the maximum of HAVAC_CUDA_SORT_STATIC_MAX_HITS = 2^20 hits:
+//   [0, 8 Mi)            keys, buffer A (the input is copied here and turned into keys in place)
+//   [8 Mi, 16 Mi)        keys, buffer B (the radix passes go A -> B -> A ...)
+//   [16 Mi, 16 Mi+256 Ki) digit counts, 256 digits x (2^20 / TILE = 256 tiles) x 4
+//   [.., +256)           OR / AND of all keys (which digits vary)
+// All calls share the array and it keeps the last call's contents: the OR/AND pair is the only part a call reads
+// before writing, and it is re-initialised by every call; keys and counts are fully overwritten over [0, n) /
+// [0, 256 * tiles) before they are read. Calls that overlap ON THE GPU (two streams, two host threads) would race
+// on the array: the entry point holds a per-process mutex and returns only after its stream has drained, so calls
+// through it cannot overlap; nothing else may use the array.
+namespace {
+
+constexpr unsigned long long STATIC_MAX_HITS = HAVAC_CUDA_SORT_STATIC_MAX_HITS;
+constexpr size_t STATIC_KEYS_BYTES = (size_t)STATIC_MAX_HITS * 8;
+constexpr size_t STATIC_MAX_TILES = (STATIC_MAX_HITS + TILE - 1) / TILE;
+constexpr size_t STATIC_COUNTS_BYTES = 256 * STATIC_MAX_TILES * sizeof(unsigned);
+constexpr size_t STATIC_OFF_B = STATIC_KEYS_BYTES;
+constexpr size_t STATIC_OFF_COUNTS = 2 * STATIC_KEYS_BYTES;
+constexpr size_t STATIC_OFF_ORAND = STATIC_OFF_COUNTS + STATIC_COUNTS_BYTES;
+constexpr size_t STATIC_SCRATCH_BYTES = STATIC_OFF_ORAND + 256;
+static_assert(STATIC_OFF_B % 256 == 0 && STATIC_OFF_COUNTS % 256 == 0 && STATIC_OFF_ORAND % 256 == 0, "sub-buffers stay 256-byte aligned");
+
+// In host code this NAME is a host-side stand-in for the symbol, not a device address: kernels get the pointer
+// that cudaGetSymbolAddress returns (static_scratch_on below), never `g_sortScratch` itself.
+static __device__ __align__(256) unsigned char g_sortScratch[STATIC_SCRATCH_BYTES];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+std::mutex g_staticMutex;                           // one call at a time per process: the array is shared
+unsigned char* g_staticAddr[STATIC_MAX_DEVICES];    // device address of g_sortScratch per device ordinal, looked up once
+
+// The device address of the scratch array on `dev`; `dev` must be the current device (the symbol has one
+// instance per device, and the lookup answers for the current one).
+cudaError_t static_scratch_on(int dev, unsigned char** out) {
+  if (!g_staticAddr[dev]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_sortScratch);
+    if (e != cudaSuccess) return e;
+    g_staticAddr[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = g_staticAddr[dev];
+  return cudaSuccess;
+}
+
+}  // namespace
+
+// CK for an entry point without a client: the text goes where havac_cuda_create's goes (havac_cuda_last_error(NULL))
+#define CKS(call)                                                                                              \
+  do {                                                                                                         \
+    cudaError_t e_ = (call);                                                                                   \
+    if (e_ != cudaSuccess)                                                                                     \
+      return havac_fail(nullptr, HAVAC_CUDA_E_RUNTIME, std::string("havac_cuda_sort_hits_static: " #call ": ") + cudaGetErrorString(e_)); \
+  } while (0)
+
+extern "C" int havac_cuda_sort_hits_static(uint32_t deviceIndex, const uint64_t* hitsIn, uint64_t n, uint64_t* hitsOut, void* stream) {
+  havac_cuda_client* const c = nullptr;  // no client: error texts go to the calling thread's slot, havac_cuda_last_error(NULL)
+  if (n > STATIC_MAX_HITS)
+    return havac_fail(c, HAVAC_CUDA_E_LENGTH, "havac_cuda_sort_hits_static: " + std::to_string(n) + " hits exceed the static scratch's maximum of " +
+                                                  std::to_string(STATIC_MAX_HITS) + " (HAVAC_CUDA_SORT_STATIC_MAX_HITS); sort through a client instead");
+  if (n == 0) return HAVAC_CUDA_OK;
+  if (!hitsIn || !hitsOut) return havac_fail(c, HAVAC_CUDA_E_INVALID, "havac_cuda_sort_hits_static: null hit array");
+  if (deviceIndex >= (uint32_t)STATIC_MAX_DEVICES) return havac_fail(c, HAVAC_CUDA_E_INVALID, "havac_cuda_sort_hits_static: device index out of range");
+  std::lock_guard<std::mutex> lock(g_staticMutex);
+  CKS(cudaSetDevice((int)deviceIndex));
+  unsigned char* base = nullptr;
+  CKS(static_scratch_on((int)deviceIndex, &base));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  unsigned long long* const bufA = reinterpret_cast<unsigned long long*>(base);
+  unsigned long long* const bufB = reinterpret_cast<unsigned long long*>(base + STATIC_OFF_B);
+  unsigned* const dCounts = reinterpret_cast<unsigned*>(base + STATIC_OFF_COUNTS);
+  unsigned long long* const dOrAnd = reinterpret_cast<unsigned long long*>(base + STATIC_OFF_ORAND);
+  const unsigned nBlocks = (unsigned)((n + TILE - 1) / TILE);
+  // cudaMemcpyDefault: hitsIn / hitsOut may be device or host memory (unified addressing tells which)
+  CKS(cudaMemcpyAsync(bufA, hitsIn, n * 8, cudaMemcpyDefault, st));
+  const unsigned long long init[2] = {0ull, ~0ull};  // the one part of the scratch that must not carry over
+  CKS(cudaMemcpyAsync(dOrAnd, init, sizeof init, cudaMemcpyHostToDevice, st));
+  const unsigned grid = (unsigned)std::min<unsigned long long>((n + 255) / 256, 148ull * 16);
+  hits_to_keys<<<grid, 256, 0, st>>>(bufA, n, dOrAnd);
+  unsigned long long orAnd[2];
+  CKS(cudaMemcpyAsync(orAnd, dOrAnd, sizeof orAnd, cudaMemcpyDeviceToHost, st));
+  CKS(cudaStreamSynchronize(st));
+  const unsigned long long varying = orAnd[0] ^ orAnd[1];
+  unsigned long long* src = bufA;
+  unsigned long long* dst = bufB;
+  for (int shift = 0; shift < 64; shift += 8) {
+    if (((varying >> shift) & 255ull) == 0) continue;
+    radix_count<<<nBlocks, STHREADS, 0, st>>>(src, n, shift, dCounts, nBlocks);
+    scan_exclusive<<<1, 1024, 0, st>>>(dCounts, (unsigned long long)256 * nBlocks);
+    radix_scatter<<<nBlocks, STHREADS, 0, st>>>(src, dst, n, shift, dCounts, nBlocks);
+    std::swap(src, dst);
+  }
+  keys_to_hits<<<grid, 256, 0, st>>>(src, n);
+  CKS(cudaGetLastError());
+  CKS(cudaMemcpyAsync(hitsOut, src, n * 8, cudaMemcpyDefault, st));
+  CKS(cudaStreamSynchronize(st));
   return HAVAC_CUDA_OK;
 }

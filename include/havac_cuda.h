@@ -207,6 +207,25 @@ int havac_cuda_tile_geometry(havac_cuda_client* c, uint32_t device, int64_t* loa
  * kernel (every warp on its own) so that the streaming kernels can be tested with short tables too. */
 int havac_cuda_set_kernel(havac_cuda_client* c, const char* name);
 
+/* Emission-order sort of raw hit words that ALLOCATES NOTHING. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it). Same kernels and same result as the sort behind havac_cuda_read_hits
+ * (FPGA emission order: segment, row, cell ascending -- device/HavacHls.cpp:131-162), but its scratch (two key
+ * buffers, digit counts) lives in a file-scope device array of the library instead of cudaMalloc'ed buffers, so the
+ * call makes no cudaMalloc / cudaFree / allocating library call. Every GPU that loads the library holds that array
+ * (16.25 MiB) until the process exits, and it bounds the size: n > HAVAC_CUDA_SORT_STATIC_MAX_HITS -> E_LENGTH.
+ *   deviceIndex : CUDA device ordinal; becomes the current device.
+ *   hitsIn      : n raw hit words, device OR host memory (unified addressing decides); not modified.
+ *   hitsOut     : n words, device or host memory; may equal hitsIn.
+ *   stream      : a cudaStream_t of that device, or NULL for the default stream. The call returns after the stream
+ *                 has drained (it reads one word back between its kernels), so hitsOut is complete on return.
+ * No client handle: the text of a failure is read with havac_cuda_last_error(NULL) on the calling thread.
+ * All calls share the one array per device and it keeps the last call's contents (what must start clean is
+ * re-initialised by every call). Calls through this entry point are serialised by a mutex inside the library; work
+ * that overlaps ON THE GPU with a call and touches the array (there is no other door to it) would race. */
+#define HAVAC_CUDA_SORT_STATIC_MAX_HITS (1u << 20)
+int havac_cuda_sort_hits_static(uint32_t deviceIndex, const uint64_t* hitsIn, uint64_t n, uint64_t* hitsOut, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
