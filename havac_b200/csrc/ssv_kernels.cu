@@ -201,7 +201,7 @@ constexpr int BLOCK_ROWS = SSV_BLOCK_ROWS;          // rows unrolled in one bloc
 constexpr int NSLOT = (W + 2 * TC) / 32;            // 32-symbol groups the window ring holds
 static_assert(BLOCK_ROWS == 32 && R == 16, "the ring layout assumes 32 diagonals and 32 rows per thread-block");
 static_assert(TC % BLOCK_ROWS == 0, "row chunk must hold whole blocks");
-static_assert(TC % 64 == 0 && TC / 64 <= THREADS, "chunk refill is done by the first TC/64 threads, 64 symbols each");
+static_assert(TC % 64 == 0, "the ring is extended 64 symbols per lane and pass");
 static_assert((W + 2 * TC) % 32 == 0, "ring must hold whole 32-symbol groups");
 
 // Shared memory of one CTA (dynamic; ~96 KB at 2048-row chunks, two CTAs per SM).
@@ -212,20 +212,18 @@ static_assert((W + 2 * TC) % 32 == 0, "ring must hold whole 32-symbol groups");
 //         windows a thread needs for four consecutive rows are one LDS.128, and the 32 lanes of a
 //         warp (32 symbols apart) read 32 consecutive uint4 -- conflict-free.
 //  tab  : double-buffered score-table chunks (TMA bulk copies).
-//  seqStage : the packed sequence words that extend the ring for the chunk after next, copied
-//         HBM -> shared memory by cp.async while the current chunk computes (no registers held).
 //  ckpt : the thread's 16 state registers at the start of the current superblock, for the exact
 //         replay (kept in shared memory so the hot loop carries no copies of them).
+//  done : warps that are through with the chunk in tab[b] (and with the TC oldest symbols of the ring). The warp that
+//         makes it WARPS refills both for the chunk after next; nobody waits for it before that chunk begins.
 struct __align__(16) FastSmem {
   uint4 ring[8][NSLOT];
   uint2 tab[2][TC];
   uint4 ckpt[R / 4][THREADS];
-  uint4 seqStage[2][TC / 64 + 1];  // packed symbols of the chunk after next (cp.async), double buffered
-  unsigned long long mbar[2];
+  unsigned long long mbar[2];  // "chunk staged": the TMA's bytes, armed by the warp that also extended the ring
   unsigned int nextTile;
-  // abort flag as seen by thread 0: [0], [1] written before the end-of-chunk barrier of even / odd chunks and read
-  // by everyone after it; [2] written in the tile prologue. A slot is rewritten two barriers after it was read.
-  int abortSeen[3];
+  unsigned int done[2];
+  int abortSeen;  // set (never cleared) by whoever polls the device's abort flag: tile prologue, chunk refill
 };
 
 // geometry of the short-table kernel (its description is at the kernel)
@@ -286,11 +284,6 @@ __device__ __forceinline__ uint4 load_seq_vec(const SsvParams& prm, long long wi
   const long long nWords = prm.nLoad >> 4;
   if (wi >= 0 && wi + 4 <= nWords) return __ldg(reinterpret_cast<const uint4*>(prm.seqPacked + wi));
   return make_uint4(0u, 0u, 0u, 0u);
-}
-
-// 16-byte asynchronous copy global -> shared (SASS: LDGSTS); srcBytes = 0 zero-fills instead.
-__device__ __forceinline__ void cp_async16(void* dst, const void* src, uint32_t srcBytes) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(srcBytes) : "memory");
 }
 
 // PRMT with the raw PTX semantics (CUDA's __byte_perm would first AND the selector with
@@ -571,7 +564,7 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
     mbar_init(&sm.mbar[0], 1);
     mbar_init(&sm.mbar[1], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    sm.abortSeen[0] = sm.abortSeen[1] = sm.abortSeen[2] = 0;
+    sm.abortSeen = 0;
     sm.nextTile = atomicAdd(prm.tileCounter, 1u);
   }
   __syncthreads();
@@ -607,7 +600,8 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
     // --- prologue: queue the first two table chunks, fill the ring, load the windows --------
     if (tid == 0) {
       sm.nextTile = atomicAdd(prm.tileCounter, 1u);
-      sm.abortSeen[2] = *prm.abortFlag;
+      if (*prm.abortFlag) sm.abortSeen = 1;
+      sm.done[0] = sm.done[1] = 0;
       for (int i = 0; i < 2 && c0 + i < c1; i++) {
         mbar_expect_tx(&sm.mbar[i], TC * sizeof(uint2));
         tma_load_1d(sm.tab[i], prm.tab16 + (size_t)(c0 + i) * TC, TC * sizeof(uint2), &sm.mbar[i]);
@@ -623,7 +617,7 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
         ring_fill64(&sm.ring[0][0], NSLOT, p0 + 64u * (uint32_t)i, load_seq_vec(prm, wFill0 + 4 * i), load_seq_word(prm, wFill0 + 4 * i + 4));
     }
     __syncthreads();
-    aborted = sm.abortSeen[2] != 0;  // CTA-uniform: written before the barrier above
+    aborted = *(volatile int*)&sm.abortSeen != 0;  // CTA-uniform: written before the barrier above
     if (aborted) {  // drain the table chunks queued above, then leave
       for (int i = 0; i < 2 && c0 + i < c1; i++) mbar_wait(&sm.mbar[i], (mbarPhase >> i) & 1u);
       break;
@@ -644,20 +638,19 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
     g = (g + 1 == (uint32_t)NSLOT) ? 0u : g + 1;  // slot the first block loads its new windows from
 
     // --- main loop over row chunks -----------------------------------------------------------
+    // The warps of a CTA do NOT meet between chunks. A warp waits for "chunk staged" (the TMA's bytes and the ring
+    // extension that goes with them), runs the chunk's blocks, and counts itself off the chunk; the warp that counts
+    // last -- the one everybody would have waited for at a barrier -- extends the ring and queues the table for the
+    // chunk after next, which re-use what the finished chunk occupied. So a warp can be up to two chunks ahead of the
+    // slowest one before it has to wait, and what a warp loses to replays in one chunk it can make up in the next.
     for (int c = c0; c < c1; c++) {
       const int buf = (c - c0) & 1;
-      // prefetch the packed symbols that extend the ring for chunk c+2: cp.async into shared memory
-      // now, expanded into ring windows after this chunk's compute
-      const uint32_t sRefill = (uint32_t)W + (uint32_t)(c + 2) * TC;
-      const bool doRefill = c + 2 < c1;
-      if (doRefill && tid <= TC / 64) {  // one vector more than the chunk: the last window needs the word after it
-        const long long wi = ((D0 + (long long)sRefill) >> 4) + 4 * tid;
-        const bool inside = wi >= 0 && wi + 4 <= (prm.nLoad >> 4);
-        cp_async16(&sm.seqStage[buf][tid], prm.seqPacked + (inside ? wi : 0), inside ? 16u : 0u);
-      }
-      asm volatile("cp.async.commit_group;" ::: "memory");
       mbar_wait(&sm.mbar[buf], (mbarPhase >> buf) & 1u);
       mbarPhase ^= 1u << buf;
+      if (*(volatile int*)&sm.abortSeen != 0) {  // a refill found the abort flag up: this chunk was never staged
+        aborted = true;
+        break;
+      }
 
       // Per block of 32 rows: checkpoint, the block, one look at the states. Everything around the block is kept in
       // 32-bit registers and as short as it can be: these instructions queue for the same (saturated) ALU pipe as the
@@ -704,24 +697,41 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
         }
       }
 
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
-      if (tid == 0 && *prm.abortFlag) sm.abortSeen[c & 1] = 1;  // before the barrier: every thread reads the same value after it
-      __syncthreads();  // all reads of tab[buf] and of the ring part about to be recycled are done; seqStage[buf] landed
-      aborted = aborted || sm.abortSeen[c & 1] != 0;
-      // the table buffers of a tile that stops here are not refilled: no TMA may be in flight when the CTA exits
-      if (tid == 0 && !aborted && c + 2 < c1) {
-        mbar_expect_tx(&sm.mbar[buf], TC * sizeof(uint2));
-        tma_load_1d(sm.tab[buf], prm.tab16 + (size_t)(c + 2) * TC, TC * sizeof(uint2), &sm.mbar[buf]);
+      if (c + 2 < c1) {
+        // through with tab[buf] and with ring offsets [c TC, (c + 1) TC): count this warp off
+        __syncwarp();
+        unsigned last = 0;
+        if ((tid & 31) == 0) {
+          __threadfence_block();  // this warp's reads, before the count that lets another warp overwrite them
+          last = atomicAdd(&sm.done[buf], 1u) == (unsigned)(THREADS / 32 - 1) ? 1u : 0u;
+          __threadfence_block();
+        }
+        last = __shfl_sync(FULL, last, 0);
+        if (last) {
+          // the ring's windows of offsets [W + (c + 2) TC, W + (c + 3) TC), straight from the packed sequence ...
+          const uint32_t sRefill = (uint32_t)W + (uint32_t)(c + 2) * TC;
+          const long long wFill = (D0 + (long long)sRefill) >> 4;
+          for (int i = tid & 31; i < TC / 64; i += 32)
+            ring_fill64(&sm.ring[0][0], NSLOT, sRefill + 64u * (uint32_t)i, load_seq_vec(prm, wFill + 4 * i), load_seq_word(prm, wFill + 4 * i + 4));
+          __syncwarp();
+          // ... then the table chunk; its arrival on the barrier publishes the windows with it (release / acquire).
+          // With the abort flag up nothing is queued -- no TMA may be in flight when the CTA exits -- and the waiters
+          // are let through to find abortSeen.
+          if ((tid & 31) == 0) {
+            sm.done[buf] = 0;
+            if (*prm.abortFlag) {
+              *(volatile int*)&sm.abortSeen = 1;
+              asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&sm.mbar[buf])) : "memory");
+            } else {
+              mbar_expect_tx(&sm.mbar[buf], TC * sizeof(uint2));
+              tma_load_1d(sm.tab[buf], prm.tab16 + (size_t)(c + 2) * TC, TC * sizeof(uint2), &sm.mbar[buf]);
+            }
+          }
+        }
       }
-      if (aborted) {
-        // chunk c+1 (if any) was queued two chunks ago: wait for it, so that nothing is in flight at exit
-        if (c + 1 < c1) mbar_wait(&sm.mbar[buf ^ 1], (mbarPhase >> (buf ^ 1)) & 1u);
-        break;
-      }
-      if (doRefill && tid < TC / 64)
-        ring_fill64(&sm.ring[0][0], NSLOT, sRefill + 64u * (uint32_t)tid, sm.seqStage[buf][tid], sm.seqStage[buf][tid + 1].x);
     }
-    __syncthreads();
+    __syncthreads();  // the next tile's prologue rewrites the ring and both table buffers
+    aborted = *(volatile int*)&sm.abortSeen != 0;  // CTA-uniform after the barrier (a warp may have finished the tile without seeing it)
     if (aborted) break;
   }
   if (tid == 0 && aborted) atomicOr(prm.status, SSV_STATUS_ABORTED);
