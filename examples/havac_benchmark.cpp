@@ -64,11 +64,12 @@ int main(int argc, char** argv) {
         "{\"fasta\": \"%s\", \"hmm\": \"%s\", \"p_value\": %g, \"symbols\": %.0f, \"records\": %llu, \"models\": %zu, "
         "\"rows\": %llu, \"hits\": %zu, \"build_s\": %.4f, \"load_phmm_s\": %.4f, \"load_sequence_s\": %.4f, "
         "\"run_s\": %.4f, \"get_hits_s\": %.4f, \"total_s\": %.4f, \"device_ms\": %.3f, \"gcups_device\": %.1f, "
-        "\"gcups_whole_program\": %.1f",
+        "\"gcups_whole_program\": %.1f, \"run_us\": %.1f, \"get_hits_us\": %.1f",
         fastaSrc.c_str(), phmmSrc.c_str(), pValue, symbols, (unsigned long long)havac->sequences().numSequences(),
         (size_t)havac->phmms().count(), (unsigned long long)rows, hits.size(), seconds(t0, t1), seconds(t1, t2),
         seconds(t2, t3), seconds(t3, t4), seconds(t4, t5), seconds(t0, t5), deviceMs,
-        symbols * (double)rows / (deviceMs * 1e-3) / 1e9, symbols * (double)rows / seconds(t0, t5) / 1e9);
+        symbols * (double)rows / (deviceMs * 1e-3) / 1e9, symbols * (double)rows / seconds(t0, t5) / 1e9, seconds(t3, t4) * 1e6,
+        seconds(t4, t5) * 1e6);
     if (both)
       std::printf(", \"crick_hits\": %zu, \"crick_reverse_s\": %.4f, \"crick_run_s\": %.4f, \"crick_get_hits_s\": %.4f", crickHits,
                   crickReverse, crickRun, crickGet);

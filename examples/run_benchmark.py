@@ -70,6 +70,15 @@ def main():
         synth.write_hmm(hmm, models)
         run(exe, fa, hmm, {"case": "configs[1] from files: 100 Mbp x 100 models"})
         run(exe, fa, hmm, {"case": "configs[1] from files, both strands (reverse complement made on the device)"}, both=True)
+        # (a') configs[0], the reference's own CPU-runnable case: 1 Mbp x one 200-position model; run_us is the latency
+        # of Havac::runHardwareClient (launch, wait), get_hits_us that of getHitsFromFinishedRun
+        sym = synth.random_symbols(1, 1_000_000)
+        models = synth.random_models(1, [200])
+        synth.plant_homologs(1, sym, models, copies=10)
+        fa1, hmm1 = os.path.join(tmp, "c1.fa"), os.path.join(tmp, "c1.hmm")
+        synth.write_fasta(fa1, [sym])
+        synth.write_hmm(hmm1, models)
+        run(exe, fa1, hmm1, {"case": "configs[0] from files: 1 Mbp x 1 model of 200 positions"})
         # (b) the published series' shape
         sym = synth.random_symbols(22, 50_800_000)
         fa = os.path.join(tmp, "chr22_like.fa")

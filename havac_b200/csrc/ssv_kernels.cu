@@ -204,7 +204,18 @@ static_assert(TC % BLOCK_ROWS == 0, "row chunk must hold whole blocks");
 static_assert(TC % 64 == 0, "the ring is extended 64 symbols per lane and pass");
 static_assert((W + 2 * TC) % 32 == 0, "ring must hold whole 32-symbol groups");
 
-// Shared memory of one CTA (dynamic; ~96 KB at 2048-row chunks, two CTAs per SM).
+constexpr int WARPS = THREADS / 32;
+// Hits on their way out. A hit is found by ONE lane deep inside the replay; taking its place in the device's hit
+// list there costs an atomic on one global counter whose answer the lane has to wait for (a microsecond, with the
+// other 31 lanes idle). Instead the lane takes a place in its warp's stage with a shared-memory atomic, and the
+// warp moves the stage out -- one global atomic, coalesced stores -- when it is half full or the tile ends.
+constexpr int HSTAGE = 240;  // hit words per warp (what two CTAs per SM leave of the shared memory)
+struct __align__(16) HitStage {
+  unsigned long long hit[WARPS][HSTAGE];
+  unsigned int count[WARPS];  // places taken; may run past HSTAGE (those hits went straight to the list)
+};
+
+// Shared memory of one CTA (dynamic; ~112 KB at 2048-row chunks, two CTAs per SM).
 //  ring : selector WINDOWS, one 32-bit entry per symbol. The entry of symbol j is
 //         sel(x_j) | sel(x_j+1) << 8 | ..., sel(x) = 0x10 + 0x22 x; PRMT reads bits [15:0], which
 //         pick the fp16 scores of x_j and x_j+1 out of the 8-byte table row. Symbol offset
@@ -216,10 +227,12 @@ static_assert((W + 2 * TC) % 32 == 0, "ring must hold whole 32-symbol groups");
 //         replay (kept in shared memory so the hot loop carries no copies of them).
 //  done : warps that are through with the chunk in tab[b] (and with the TC oldest symbols of the ring). The warp that
 //         makes it WARPS refills both for the chunk after next; nobody waits for it before that chunk begins.
+//  stage: hit words waiting for their place in the device's hit list, per warp (see HitStage)
 struct __align__(16) FastSmem {
   uint4 ring[8][NSLOT];
   uint2 tab[2][TC];
   uint4 ckpt[R / 4][THREADS];
+  HitStage stage;
   unsigned long long mbar[2];  // "chunk staged": the TMA's bytes, armed by the warp that also extended the ring
   unsigned int nextTile;
   unsigned int done[2];
@@ -230,12 +243,12 @@ struct __align__(16) FastSmem {
 constexpr int SHORT_ROWS = SSV_SHORT_ROWS;                 // rows the short-table kernel accepts (multiple of 32)
 constexpr int WARP_DIAGS = 32 * 2 * R;                     // 1024 diagonals per warp tile
 constexpr int NS_SHORT = (WARP_DIAGS + SHORT_ROWS + 64) / 32;  // 32-symbol groups per plane of a warp's ring (never wraps)
-constexpr int WARPS = THREADS / 32;
 
 struct __align__(16) ShortSmem {
   uint4 ring[WARPS][8][NS_SHORT];
   uint2 tab[SHORT_ROWS];
   uint4 ckpt[R / 4][THREADS];
+  HitStage stage;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -384,16 +397,46 @@ __device__ __forceinline__ uint2 lds_v2(uint32_t addr) {
 }
 
 // A register whose fp16 halves just reached inf at row p: report the hit(s), reset those halves
-// to 0 as the reference does (SoftSsv.cpp:44-49), return the register.
-__device__ __noinline__ uint32_t on_hit(const SsvParams& prm, uint32_t v, long long dlo, uint32_t p) {
+// to 0 as the reference does (SoftSsv.cpp:44-49), return the register. `stage` = shared-space address of the warp's
+// hit stage (HitStage::hit[warp]); its counter sits at `stageCount`.
+__device__ __noinline__ uint32_t on_hit(const SsvParams& prm, uint32_t v, long long dlo, uint32_t p, uint32_t stage, uint32_t stageCount) {
 #pragma unroll 1
   for (int h = 0; h < 2; h++) {
     if (((v >> (16 * h)) & 0xffffu) != 0x7c00u) continue;
     v &= h ? 0x0000ffffu : 0xffff0000u;
     const long long col = dlo + h + (long long)p + prm.loadBegin;
-    if (p < prm.nRows && col >= prm.colBegin && col < prm.colEnd) emit_hit_active(prm, col, p);
+    if (p < prm.nRows && col >= prm.colBegin && col < prm.colEnd) {
+      uint32_t place;
+      asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(place) : "r"(stageCount) : "memory");
+      if (place < (uint32_t)HSTAGE) {
+        const unsigned long long word = encode_hit(col, p);
+        asm volatile("st.shared.u64 [%0], %1;" ::"r"(stage + 8u * place), "l"(word) : "memory");
+      } else {
+        emit_hit_active(prm, col, p);  // stage full (a warp-block with more than 120 hits): straight to the list
+      }
+    }
   }
   return v;
+}
+
+// Moves the warp's staged hits into the device's hit list: one atomic for all of them, coalesced stores. Called by
+// the whole warp (converged).
+__device__ __noinline__ void flush_hits(const SsvParams& prm, HitStage& st) {
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncwarp();
+  unsigned n = *(volatile unsigned*)&st.count[warp];
+  if (n == 0) return;
+  if (n > (unsigned)HSTAGE) n = HSTAGE;
+  unsigned long long base = 0;
+  if (lane == 0) base = atomicAdd(prm.hitCount, (unsigned long long)n);
+  base = __shfl_sync(FULL, base, 0);
+  for (unsigned i = lane; i < n; i += 32) {
+    if (base + i < prm.hitCap) prm.hits[base + i] = st.hit[warp][i];
+    else atomicOr(prm.status, SSV_STATUS_OVERFLOW);
+  }
+  __syncwarp();
+  if (lane == 0) *(volatile unsigned*)&st.count[warp] = 0;
+  __syncwarp();
 }
 
 // SHORT: called from the short-table kernel (the warp's private ring, the whole table at `tab`) or from the streaming
@@ -403,13 +446,15 @@ extern __shared__ __align__(16) unsigned char smemRaw[];
 template <bool SHORT>
 __device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, const uint2* tab, uint32_t infMask, bool edge,
                                             long long d0, long long D0, uint32_t pb, uint32_t nRowsReplay) {
-  struct Geom { uint32_t ckBase, ringBase, nslot, tabBase, tabMask; } geo;
+  struct Geom { uint32_t ckBase, ringBase, nslot, tabBase, tabMask, stage, stageCount; } geo;
   if constexpr (SHORT) {
     ShortSmem& sm = *reinterpret_cast<ShortSmem*>(smemRaw);
-    geo = {smem_u32(&sm.ckpt[0][0]), smem_u32(&sm.ring[threadIdx.x >> 5][0][0]), (uint32_t)NS_SHORT, smem_u32(tab), 0xffffffffu};
+    geo = {smem_u32(&sm.ckpt[0][0]), smem_u32(&sm.ring[threadIdx.x >> 5][0][0]), (uint32_t)NS_SHORT, smem_u32(tab), 0xffffffffu,
+           smem_u32(&sm.stage.hit[threadIdx.x >> 5][0]), smem_u32(&sm.stage.count[threadIdx.x >> 5])};
   } else {
     FastSmem& sm = *reinterpret_cast<FastSmem*>(smemRaw);
-    geo = {smem_u32(&sm.ckpt[0][0]), smem_u32(&sm.ring[0][0]), (uint32_t)NSLOT, smem_u32(tab), (uint32_t)TC - 1u};
+    geo = {smem_u32(&sm.ckpt[0][0]), smem_u32(&sm.ring[0][0]), (uint32_t)NSLOT, smem_u32(tab), (uint32_t)TC - 1u,
+           smem_u32(&sm.stage.hit[threadIdx.x >> 5][0]), smem_u32(&sm.stage.count[threadIdx.x >> 5])};
   }
   // Registers do not cross this call: the caller says which of its registers hold an inf
   // (infMask), the exact end state of every replayed register is written over its checkpoint
@@ -445,7 +490,7 @@ __device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, const uint2* t
         const long long j = dlo + (long long)p;
         if (j < 0) v &= 0xffff0000u;
         if (j + 1 < 0) v = 0u;
-        if (has_inf(v)) v = on_hit(prm, v, dlo, p);
+        if (has_inf(v)) v = on_hit(prm, v, dlo, p, geo.stage, geo.stageCount);
       }
     } else {
       // Sixteen rows at a time: the lookups do not depend on the state, so their loads pipeline,
@@ -475,7 +520,7 @@ __device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, const uint2* t
 #pragma unroll
         for (uint32_t i = 0; i < 16; i++) {
           v = hfma2_relu_add(m[i], v);
-          if (has_inf(v)) v = on_hit(prm, v, dlo, pb + rb + i);
+          if (has_inf(v)) v = on_hit(prm, v, dlo, pb + rb + i, geo.stage, geo.stageCount);
         }
       }
     }
@@ -567,6 +612,7 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
     sm.abortSeen = 0;
     sm.nextTile = atomicAdd(prm.tileCounter, 1u);
   }
+  if ((tid & 31) == 0) sm.stage.count[tid >> 5] = 0;
   __syncthreads();
   bool aborted = false;
 
@@ -694,6 +740,8 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
 #pragma unroll
           for (int k = 0; k < R; k++)
             if ((changed >> k) & 1u) w[k] = ck[((k >> 2) * THREADS + tid) * 4 + (k & 3)];
+          __syncwarp();
+          if (*(volatile unsigned*)&sm.stage.count[tid >> 5] >= (unsigned)(HSTAGE / 2)) flush_hits(prm, sm.stage);
         }
       }
 
@@ -734,6 +782,7 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
     aborted = *(volatile int*)&sm.abortSeen != 0;  // CTA-uniform after the barrier (a warp may have finished the tile without seeing it)
     if (aborted) break;
   }
+  flush_hits(prm, sm.stage);
   if (tid == 0 && aborted) atomicOr(prm.status, SSV_STATUS_ABORTED);
   if (tid == 0 && blockIdx.x == 0) *prm.smCycles = (unsigned long long)(clock64() - clk0);
 }
@@ -756,6 +805,7 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_short_kernel
   // the whole table, once per CTA (pad rows of the device table are -128: they can never hit)
   const uint32_t rowsPad = (prm.nRows + BLOCK_ROWS - 1) / BLOCK_ROWS * BLOCK_ROWS;
   for (uint32_t r = tid; r < rowsPad; r += THREADS) sm.tab[r] = __ldg(prm.tab16 + r);
+  if (lane == 0) sm.stage.count[warp] = 0;
   __syncthreads();
 
   uint4* ring = &sm.ring[warp][0][0];
@@ -829,10 +879,13 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_short_kernel
 #pragma unroll
         for (int k = 0; k < R; k++)
           if ((changed >> k) & 1u) w[k] = ck[((k >> 2) * THREADS + tid) * 4 + (k & 3)];
+        __syncwarp();
+        if (*(volatile unsigned*)&sm.stage.count[warp] >= (unsigned)(HSTAGE / 2)) flush_hits(prm, sm.stage);
       }
     }
     __syncwarp();  // every lane has read its last windows before the ring is refilled
   }
+  flush_hits(prm, sm.stage);
   if (lane == 0 && aborted) atomicOr(prm.status, SSV_STATUS_ABORTED);
   if (tid == 0 && blockIdx.x == 0) *prm.smCycles = (unsigned long long)(clock64() - clk0);
 }

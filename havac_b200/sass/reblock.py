@@ -350,6 +350,13 @@ def reschedule(block, log):
         q = lds_by_uid[uid].d
         if q not in quads and all(q + i in pool for i in range(4)):
             quads.append(q)
+    # ... and where ptxas got by with one (it may recycle a single quad when registers are short), any other 4-aligned
+    # group of registers this plan is free to use
+    for q in range(0, 252, 4):
+        if len(quads) >= 2:
+            break
+        if q not in quads and all(q + i in pool for i in range(4)):
+            quads.append(q)
     need(len(quads) >= 2 and all(q % 2 == 0 for q in quads), "fewer than two (even-aligned) table quads")
     quads = quads[:2]
     for q in quads:
