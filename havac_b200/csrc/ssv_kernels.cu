@@ -390,6 +390,11 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
   return v;
 }
+__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
 __device__ __forceinline__ uint2 lds_v2(uint32_t addr) {
   uint2 v;
   asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
@@ -499,16 +504,19 @@ __device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, const uint2* t
       // nRowsReplay is a multiple of 32.
 #pragma unroll 1
       for (uint32_t rb = 0; rb < nRowsReplay; rb += 16) {
+        // s0 is even (32 per thread, 2 per register, 32 per block) and so is the row: two consecutive symbols' windows
+        // are one 64-bit half of a ring entry, two consecutive table rows one 128-bit load
         const uint32_t sA = s0 + rb, qA = sA >> 5;
         const uint32_t slotA = qA % NSL, slotB = slotA + 1 == NSL ? 0u : slotA + 1;
         uint32_t m[16];
 #pragma unroll
-        for (uint32_t i = 0; i < 16; i++) {
+        for (uint32_t i = 0; i < 16; i += 2) {
           const uint32_t sy = sA + i;
           const uint32_t sl = (sy >> 5) == qA ? slotA : slotB;
-          const uint32_t sel = lds_u32(ringBase + (((sy & 31u) >> 2) * NSL + sl) * 16u + (sy & 3u) * 4u);
-          const uint2 e2 = lds_v2(tabBase + ((pb + rb + i) & geo.tabMask) * 8u);
-          m[i] = prmt(e2.x, e2.y, sel);
+          const uint2 sel2 = lds_v2(ringBase + (((sy & 31u) >> 2) * NSL + sl) * 16u + (sy & 2u) * 4u);
+          const uint4 e4 = lds_v4(tabBase + ((pb + rb + i) & geo.tabMask) * 8u);
+          m[i] = prmt(e4.x, e4.y, sel2.x);
+          m[i + 1] = prmt(e4.z, e4.w, sel2.y);
         }
         uint32_t vv = v;
 #pragma unroll
