@@ -414,12 +414,15 @@ def run_gpu(args, rank, world, local_rank):
     barrier()
     t0 = time.perf_counter()
     step_ms = []
+    slowest = (0.0, {})
     for _ in range(args.steps):
         ts = time.perf_counter()
         hits, whole = e2e_step()
         step_ms.append(round((time.perf_counter() - ts) * 1e3, 2))
+        if step_ms[-1] > slowest[0]:
+            slowest = (step_ms[-1], dict(phases))
     barrier()
-    log(f"[rank {rank}] e2e wall per step (ms): {step_ms}")
+    log(f"[rank {rank}] e2e wall per step (ms): {step_ms}; phases of the slowest step: {slowest[1]}")
     e2e_s = reduce((time.perf_counter() - t0) / args.steps, "MAX")
     h2d1, d2h1 = client.transferStats()
     log(f"[rank {rank}] e2e phases of the last step (ms): {phases}")
@@ -514,7 +517,8 @@ def run_gpu(args, rank, world, local_rank):
                        "symbols_per_gpu": SEQ_PER_GPU, "rows": rows, "hits": int(hits_all),
                        "parallelism": f"sequence axis sharded over {world} GPU(s), halo rows-1, no collective"},
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "ms_per_step": e2e_s * 1e3, "phases_ms": phases,
+                    "ms_per_step": e2e_s * 1e3, "ms_per_step_median": float(np.median(step_ms)), "ms_steps": step_ms,
+                    "phases_ms": phases, "phases_ms_of_slowest_step": slowest[1],
                     "hits_on_rank0_after_gather": gathered["hits"],
                     "host_gather_bytes_per_step": int(gathered["bytes"] / args.steps),
                     "ends_with": "one hit list in emission order in rank 0's host memory"},

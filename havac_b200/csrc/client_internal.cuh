@@ -58,6 +58,10 @@ struct DeviceCtx {
   unsigned long long hitCount = 0;
   int status = 0;
   bool hitsSorted = false;  // dHits already put into emission order (hit_postprocess.cu)
+  // scratch of the emission-order sort (second key buffer, digit counts, OR/AND word): kept between runs and grown
+  // when a run has more hits, so that reading the hit list costs no cudaMalloc / cudaFree in the steady state
+  void* sortScratch = nullptr;
+  size_t sortScratchCap = 0;
   // how the last launch cut its work (havac_cuda_tile_geometry)
   long long lastLoadBegin = 0, lastDiagBegin = 0;
   uint32_t lastTiles = 0, lastTileDiags = 0;

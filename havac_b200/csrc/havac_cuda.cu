@@ -340,6 +340,7 @@ int havac_cuda_destroy(havac_cuda_client* c) {
     free_sequence(d);
     free_table(d);
     if (d.dHits) cudaFree(d.dHits);
+    if (d.sortScratch) cudaFree(d.sortScratch);
     if (d.dCtl) cudaFree(d.dCtl);
     if (d.hostRes) cudaFreeHost(d.hostRes);
     if (d.evDone) cudaEventDestroy(d.evDone);

@@ -78,29 +78,52 @@ __global__ void __launch_bounds__(STHREADS) radix_count(const unsigned long long
   counts[(size_t)threadIdx.x * nBlocks + blockIdx.x] = hist[threadIdx.x];
 }
 
-// one CTA: exclusive scan of `total` 32-bit counters in place
+// one CTA: exclusive scan of `total` 32-bit counters in place (total is a multiple of 4: 256 digits x tiles, and the
+// array is 16-byte aligned). 4096 counters per round: one coalesced 128-bit load per thread, a shuffle scan inside
+// each warp, the 32 warp totals scanned by warp 0, a running carry across rounds.
 __global__ void __launch_bounds__(1024) scan_exclusive(unsigned* __restrict__ v, unsigned long long total) {
-  __shared__ unsigned part[1024];
-  const unsigned long long per = (total + 1023) / 1024;
-  const unsigned long long a = min((unsigned long long)threadIdx.x * per, total), b = min(a + per, total);
-  unsigned s = 0;
-  for (unsigned long long i = a; i < b; i++) s += v[i];
-  part[threadIdx.x] = s;
+  __shared__ unsigned warpSum[32];
+  __shared__ unsigned carry;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry = 0;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    unsigned acc = 0;
-    for (int t = 0; t < 1024; t++) {
-      const unsigned mine = part[t];
-      part[t] = acc;
-      acc += mine;
+  uint4* v4 = reinterpret_cast<uint4*>(v);
+  const unsigned long long quads = total / 4;
+  for (unsigned long long base = 0; base < quads; base += 1024) {
+    const unsigned long long i = base + threadIdx.x;
+    uint4 x = i < quads ? v4[i] : make_uint4(0u, 0u, 0u, 0u);
+    const unsigned mine = x.x + x.y + x.z + x.w;
+    unsigned incl = mine;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const unsigned up = __shfl_up_sync(FULLMASK, incl, off);
+      if (lane >= (unsigned)off) incl += up;
     }
-  }
-  __syncthreads();
-  s = part[threadIdx.x];
-  for (unsigned long long i = a; i < b; i++) {
-    const unsigned c = v[i];
-    v[i] = s;
-    s += c;
+    if (lane == 31) warpSum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      const unsigned t = warpSum[lane];
+      unsigned ti = t;
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const unsigned up = __shfl_up_sync(FULLMASK, ti, off);
+        if (lane >= (unsigned)off) ti += up;
+      }
+      warpSum[lane] = ti - t;  // exclusive offset of each warp inside the round
+    }
+    __syncthreads();
+    unsigned at = carry + warpSum[warp] + (incl - mine);
+    if (i < quads) {
+      uint4 o;
+      o.x = at;
+      o.y = at + x.x;
+      o.z = o.y + x.y;
+      o.w = o.z + x.z;
+      v4[i] = o;
+    }
+    __syncthreads();  // everyone has read carry and warpSum
+    if (threadIdx.x == 1023) carry = at + mine;  // thread 1023's inclusive end = the round's total on top of the carry
+    __syncthreads();
   }
 }
 
@@ -189,18 +212,30 @@ int havac_sort_hits_on_device(havac_cuda_client* c, DeviceCtx& d) {
   if (n >= (1ull << 32)) return havac_fail(c, HAVAC_CUDA_E_LENGTH, "more than 2^32 hits on one device");
   CK(cudaSetDevice(d.dev));
   cudaStream_t st = d.stream;
-  Frees frees;
-  auto dalloc = [&](void** p, size_t bytes) {
-    cudaError_t e = cudaMalloc(p, bytes);
-    if (e == cudaSuccess) frees.p.push_back(*p);
-    return e;
-  };
   const unsigned nBlocks = (unsigned)((n + TILE - 1) / TILE);
-  unsigned long long *dTmp = nullptr, *dOrAnd = nullptr;
-  unsigned* dCounts = nullptr;
-  CK(dalloc((void**)&dTmp, n * 8));
-  CK(dalloc((void**)&dCounts, (size_t)256 * nBlocks * sizeof(unsigned)));
-  CK(dalloc((void**)&dOrAnd, 16));
+  // one allocation, kept on the device context: [keys n x 8 | counts 256 x tiles x 4 | OR/AND 16], 256-byte aligned parts
+  const size_t keysBytes = ((size_t)n * 8 + 255) & ~(size_t)255;
+  const size_t countsBytes = ((size_t)256 * nBlocks * sizeof(unsigned) + 255) & ~(size_t)255;
+  const size_t need = keysBytes + countsBytes + 256;
+  if (d.sortScratchCap < need) {
+    if (d.sortScratch) cudaFree(d.sortScratch);
+    d.sortScratch = nullptr;
+    d.sortScratchCap = 0;
+    const size_t want = need + need / 2;  // room to grow without another allocation
+    cudaError_t e = cudaMalloc(&d.sortScratch, want);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      e = cudaMalloc(&d.sortScratch, need);
+      if (e != cudaSuccess) { cudaGetLastError(); return havac_fail(c, HAVAC_CUDA_E_NOMEM, "cudaMalloc(sort scratch): out of device memory"); }
+      d.sortScratchCap = need;
+    } else {
+      d.sortScratchCap = want;
+    }
+  }
+  unsigned char* const base = static_cast<unsigned char*>(d.sortScratch);
+  unsigned long long* const dTmp = reinterpret_cast<unsigned long long*>(base);
+  unsigned* const dCounts = reinterpret_cast<unsigned*>(base + keysBytes);
+  unsigned long long* const dOrAnd = reinterpret_cast<unsigned long long*>(base + keysBytes + countsBytes);
   const unsigned long long init[2] = {0ull, ~0ull};
   CK(cudaMemcpyAsync(dOrAnd, init, sizeof init, cudaMemcpyHostToDevice, st));
   const unsigned grid = (unsigned)std::min<unsigned long long>((n + 255) / 256, 148ull * 16);
