@@ -91,6 +91,32 @@ def test_hit_dense_resets():
     assert len(want) > 10_000
 
 
+def test_hit_dense_long_table_stage_overflow():
+    """Positive drift over a table of several row chunks: every warp replays block after block, its hit stage
+    (240 words in shared memory) overflows into the direct path and is flushed at the half-full mark many times,
+    while the chunks are handed from warp to warp."""
+    g = synth.rng(31, 1)
+    t = g.integers(-20, 60, size=(4200, 4)).astype(np.int8)  # 3 row chunks
+    sym = synth.random_symbols(31, 12288)
+    want = check(synth.pack_2bit(sym), t, kernels=("f16x2", "scalar"), min_hits=1_000_000)
+    assert len(want) > 1_000_000
+
+
+def test_uneven_replay_load_lets_warps_drift_chunks_apart():
+    """Only 'A' scores: stretches of poly-A make the warps that own their diagonals replay every block while the
+    other warps of the CTA never do, so the busy warps fall whole chunks behind (the streaming kernels have no
+    CTA-wide barrier between chunks; the last warp through a chunk refills it). 9000 rows = 5 chunks."""
+    g = synth.rng(32, 1)
+    rows = 9000
+    t = np.full((rows, 4), -30, dtype=np.int8)
+    t[:, 0] = g.integers(30, 50, size=rows)
+    sym = g.integers(1, 4, size=5 * 12288).astype(np.uint8)  # no 'A' at all ...
+    for at in range(3000, len(sym) - 2500, 20000):           # ... but for three stretches of 600
+        sym[at:at + 600] = 0
+    want = check(synth.pack_2bit(sym), t, kernels=("f16x2", "scalar"), min_hits=100_000)
+    assert len(want) > 100_000
+
+
 def test_extreme_scores():
     g = synth.rng(4, 1)
     t = g.choice(np.array([-128, -127, -1, 0, 1, 126, 127], dtype=np.int8), size=(500, 4))
