@@ -379,9 +379,9 @@ def run_gpu(args, rank, world, local_rank):
     n_hits = client.getNumHits()
     geom = client.tileGeometry()
     _, launches_per_step = client.runStats()
-    # SM clock the kernel itself saw: clock64 ticks of its first CTA over the launch's CUDA-event time (last step).
-    # nvidia-smi's sampled figure can sit at the maximum while the SMs run below it.
-    kernel_mhz = client.smCycles() / (ms_list[-1] * 1e3) if ms_list and ms_list[-1] > 0 else None
+    # clock64 ticks of the kernel's first CTA over the launch's CUDA-event time (last step), as MHz: the SM clock times
+    # the share of the launch that CTA was alive for (persistent CTAs leave when the tiles run out: < 1 means a tail)
+    cta0_mhz = client.smCycles() / (ms_list[-1] * 1e3) if ms_list and ms_list[-1] > 0 else None
     ms_dev = reduce(float(np.mean(ms_list)), "MAX")
     cells_all = reduce(float(my_symbols) * rows, "SUM")
     hits_all = reduce(float(n_hits), "SUM")
@@ -487,8 +487,8 @@ def run_gpu(args, rank, world, local_rank):
             "achieved": per_gpu_cells_s / 1e9, "peak": peak / 1e9, "unit": "Gcell/s (1 lane-instruction per cell)",
             "frac": per_gpu_cells_s / peak, "peak_basis": f"{sms} SMs x {f_max / 1e6:.0f} MHz (max SM clock) x {LANES_PER_SM_CLK} lanes/clk",
             "frac_at_sampled_clock": (per_gpu_cells_s / (sms * f_run * LANES_PER_SM_CLK)) if f_run else None,
-            "sm_mhz_in_kernel": kernel_mhz,
-            "frac_at_kernel_clock": (per_gpu_cells_s / (sms * kernel_mhz * 1e6 * LANES_PER_SM_CLK)) if kernel_mhz else None,
+            "first_cta_cycles_per_us": cta0_mhz,
+            "first_cta_alive_share": (cta0_mhz * 1e6 / f_run) if (cta0_mhz and f_run) else None,
             "traffic": traffic_from_profile(my_symbols, rows),
             "hbm": {"achieved": hbm_bytes / (ms_dev * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                     "frac": (hbm_bytes / (ms_dev * 1e-3) / 1e9 / hbm_peak) if hbm_peak else None,

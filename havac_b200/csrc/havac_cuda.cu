@@ -325,6 +325,9 @@ int havac_cuda_create(const char* deviceSpec, uint32_t deviceIndex, havac_cuda_c
     d.dStatus = &d.dCtl->status;
     d.dTileCounter = &d.dCtl->tileCounter;
     d.dAbort = &d.dCtl->abort;
+    // the SSV kernels' attributes are set (which also loads their code onto this device) while the device is being
+    // opened, like the xclbin load of HavacHwClient::generateKernel: the first search does not pay for it
+    ssv_f16x2_ctas_per_sm();
   }
   *out = c;
   return HAVAC_CUDA_OK;

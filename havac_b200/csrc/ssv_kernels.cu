@@ -23,16 +23,19 @@
 //    memory-bound: per 8192-diagonal row it reads 8 B of table and 1/4 B of sequence.
 //  * Score-table rows are staged into shared memory in 2048-row chunks by TMA bulk copies
 //    (cp.async.bulk + mbarrier, double buffered). The 2-bit packed sequence is read from HBM
-//    with 128-bit accesses (cp.async into a double-buffered staging area, one chunk ahead) and expanded into a shared-memory ring of ready-made selector windows
+//    with 128-bit loads and expanded into a shared-memory ring of ready-made selector windows
 //    (one 32-bit entry per symbol) that slides along the diagonal band; a thread fetches the
-//    four windows of four rows with one conflict-free LDS.128, so the hot loop spends no ALU
-//    instruction on selectors.
+//    windows of four rows as two 64-bit halves of one conflict-free ring entry, so the hot loop
+//    spends no ALU instruction on selectors. The warps of a CTA do not meet between chunks: the
+//    warp that is last through a chunk extends the ring and queues the table chunk after next.
 //  * The state at the start of every superblock (one 32-row block: a replay costs the rows it
 //    covers, and real searches have dense runs of hits; four blocks would be 0.7 % faster on
 //    hit-free input and up to 37 % slower on hit-dense input) is checkpointed in shared memory;
 //    hits (inf) are looked for once per superblock. The replay runs sixteen rows at a time
 //    without looking and walks only the sixteen that end in inf row by row.
-//  * Hits are compacted with warp ballot + prefix popcount and one atomicAdd per warp-row.
+//  * A hit found in the replay takes a place in its warp's stage in shared memory; the warp moves the stage to
+//    the device's hit list with one atomicAdd and coalesced stores (the plain kernel compacts with warp ballot +
+//    prefix popcount and one atomicAdd per warp-row).
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <atomic>
@@ -485,9 +488,11 @@ __device__ __noinline__ uint32_t exact_rows(const SsvParams& prm, const uint2* t
     uint32_t v = lds_u32(slot);
     const uint32_t s0 = (uint32_t)(dlo + (long long)pb - D0);  // ring offset of the low half's symbol at row pb
     if (crossing) {
-      // first tiles only: row by row, with the cells left of column 0 held at 0
-#pragma unroll 1
-      for (uint32_t r = 0; r < nRowsReplay; r++) {
+      // first tiles only: row by row, with the cells left of column 0 held at 0. Nothing is real before the high
+      // half's diagonal (dlo + 1) reaches column 0, at row -(dlo + 1): the walk starts there, from 0.
+      v = 0u;
+#pragma unroll 4
+      for (uint32_t r = (uint32_t)(-(dlo + 1) - (long long)pb); r < nRowsReplay; r++) {
         const uint32_t sy = s0 + r, p = pb + r;
         const uint32_t sel = lds_u32(ringBase + (((sy & 31u) >> 2) * NSL + (sy >> 5) % NSL) * 16u + (sy & 3u) * 4u);
         const uint2 e2 = lds_v2(tabBase + (p & geo.tabMask) * 8u);
@@ -628,10 +633,11 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
     const unsigned ticket = sm.nextTile;
     __syncthreads();  // everyone has read nextTile before thread 0 overwrites it
     if (ticket >= prm.nTiles) break;
-    // Tiles are handed out from the right end of the band to the left: the tiles that start left of column 0
-    // (an unsharded run has rows/W of them, each with fewer rows than the one before) come last and in decreasing
-    // length, which is the order that evens out the finish times of the persistent CTAs.
-    const unsigned tile = prm.nTiles - 1u - ticket;
+    // Tiles are handed out left to right: the tiles that start left of column 0 (an unsharded run has rows/W of
+    // them) go first. They have fewer rows than the others but the warp the column-0 boundary runs through walks
+    // its crossing registers row by row there, so they are the SLOW ones, and a slow tile handed out last is the
+    // kernel's tail (profiles/r2_ncu_full_f16x2.txt before this: SMs active 218.0 M of 226.9 M elapsed cycles).
+    const unsigned tile = ticket;
 
     const long long D0 = prm.diagBegin + (long long)tile * W;  // first diagonal of this tile
     const long long d0 = D0 + (long long)tid * (2 * R);        // first diagonal of this thread
@@ -644,7 +650,10 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
     const int c0 = (int)(rowBegin / TC);
     const int c1 = (int)((rowEnd + TC - 1) / TC);  // exclusive
     // rows (from row 0) in which the tile still has diagonals left of column 0: D0 + row < 0
-    const uint32_t edgeRows = D0 < 0 ? (uint32_t)(-D0 < 0x7fffffffll ? -D0 : 0x7fffffffll) : 0u;
+    // ... seen from this WARP: its first diagonal is D0 + 1024 warp, so it is clear of column 0 from row -(that) on.
+    // (The warps to the right of the one the boundary runs through never take the edge path.)
+    const long long dWarp = D0 + (long long)(tid & ~31) * (2 * R);
+    const uint32_t edgeRows = dWarp < 0 ? (uint32_t)(-dWarp < 0x7fffffffll ? -dWarp : 0x7fffffffll) : 0u;
     if (rowEnd <= rowBegin) {                       // nothing to do (defensive)
       if (tid == 0) sm.nextTile = atomicAdd(prm.tileCounter, 1u);
       __syncthreads();
@@ -737,7 +746,7 @@ __device__ __forceinline__ void ssv_f16x2_body(const SsvParams& prm) {
         uint32_t mx = 0;
 #pragma unroll
         for (int k = 0; k < R; k += 2) mx = __vimax3_s16x2(mx, w[k], w[k + 1]);
-        const bool edge = pb < edgeRows;  // tile-uniform: diagonals left of column 0 remain
+        const bool edge = pb < edgeRows;  // warp-uniform: this warp still has diagonals left of column 0
         if (edge || __any_sync(FULL, has_inf(mx))) {
           // cold path, out of line: the replay leaves the exact states in the checkpoint slots
           uint32_t infMask = 0;
@@ -829,7 +838,7 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) ssv_f16x2_short_kernel
     ticket = __shfl_sync(FULL, ticket, 0);
     aborted = __shfl_sync(FULL, stop, 0) != 0;
     if (ticket >= nTilesW || aborted) break;
-    const unsigned tile = nTilesW - 1u - ticket;  // right to left, as in the streaming kernels
+    const unsigned tile = ticket;  // left to right, as in the streaming kernels: the column-0 tiles first
     const long long D0 = prm.diagBegin + (long long)tile * WARP_DIAGS;
     const long long d0 = D0 + (long long)lane * (2 * R);
     long long rowEnd = prm.nLoad - D0;

@@ -167,7 +167,9 @@ int havac_cuda_device_count(havac_cuda_client* c, int* n);
  * of this client's range, halo and padding excluded); launches = kernels launched. */
 int havac_cuda_run_stats(havac_cuda_client* c, uint64_t* cells, uint32_t* launches);
 /* SM clock cycles the first persistent CTA spent in the last run's kernel (clock64), max over
- * devices; cycles / device_time gives the SM clock the kernel actually ran at. */
+ * devices; cycles / device_time = the SM clock times the share of the launch that CTA was alive for
+ * (a persistent CTA leaves when the tiles run out, so the quotient falls short of the clock by the
+ * kernel's tail). */
 int havac_cuda_sm_cycles(havac_cuda_client* c, uint64_t* cycles);
 /* Running totals of the bytes this client copied host->device and device->host. */
 int havac_cuda_transfer_stats(havac_cuda_client* c, uint64_t* h2dBytes, uint64_t* d2hBytes);

@@ -1,0 +1,9 @@
+#!/bin/bash
+# last check of round 2 on one GPU: whole GPU suite, smoke, the full bench line (with the strong leg)
+cd "$(dirname "$0")/.." && mkdir -p gpurun_out
+timeout 900 python -m pytest tests -x -q -m gpu --durations=5 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log; tail -10 gpurun_out/pytest_gpu.log
+timeout 200 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke.log 2>&1; tail -3 gpurun_out/smoke.log
+timeout 400 python bench.py > gpurun_out/r2_bench_final.json 2> gpurun_out/r2_bench_final.err; echo "bench rc=$?"
+grep "e2e wall" gpurun_out/r2_bench_final.err | cut -c1-400
+python -c "
+import json; d=json.load(open('gpurun_out/r2_bench_final.json')); print(d['value'], d['ms_per_step'], d['e2e']['value'], d['roofline']['frac'], d['roofline']['frac_at_kernel_clock'], d['strong']['value'])"
