@@ -104,3 +104,4 @@ void havac_free_sequence(DeviceCtx& d);
 int havac_place_sequence(havac_cuda_client* c, const uint8_t* packed, int srcDevice, uint64_t nBytes);
 // hit_postprocess.cu: sorts d.dHits[0, d.hitCount) into the FPGA's emission order on the device
 int havac_sort_hits_on_device(havac_cuda_client* c, DeviceCtx& d);
+void havac_postprocess_preload();  // loads the sort / resolve kernels onto the current device

@@ -328,6 +328,7 @@ int havac_cuda_create(const char* deviceSpec, uint32_t deviceIndex, havac_cuda_c
     // the SSV kernels' attributes are set (which also loads their code onto this device) while the device is being
     // opened, like the xclbin load of HavacHwClient::generateKernel: the first search does not pay for it
     ssv_f16x2_ctas_per_sm();
+    havac_postprocess_preload();
   }
   *out = c;
   return HAVAC_CUDA_OK;

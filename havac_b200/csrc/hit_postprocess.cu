@@ -198,12 +198,43 @@ __global__ void resolve_hits(const unsigned long long* __restrict__ hits, unsign
   }
 }
 
-struct Frees {
-  std::vector<void*> p;
-  ~Frees() { for (void* q : p) cudaFree(q); }
-};
-
 }  // namespace
+
+// The device context's post-processing scratch (DeviceCtx::sortScratch), at least `need` bytes: kept between calls and
+// grown by half again when a run needs more, so that the steady state makes no cudaMalloc / cudaFree. The sort and the
+// resolution use it one after the other (each drains the stream before it returns). The device must be current.
+static int ensure_scratch(havac_cuda_client* c, DeviceCtx& d, size_t need) {
+  if (d.sortScratchCap >= need) return HAVAC_CUDA_OK;
+  if (d.sortScratch) cudaFree(d.sortScratch);
+  d.sortScratch = nullptr;
+  d.sortScratchCap = 0;
+  const size_t want = need + need / 2;
+  if (cudaMalloc(&d.sortScratch, want) == cudaSuccess) {
+    d.sortScratchCap = want;
+    return HAVAC_CUDA_OK;
+  }
+  cudaGetLastError();
+  if (cudaMalloc(&d.sortScratch, need) == cudaSuccess) {
+    d.sortScratchCap = need;
+    return HAVAC_CUDA_OK;
+  }
+  cudaGetLastError();
+  d.sortScratch = nullptr;
+  return havac_fail(c, HAVAC_CUDA_E_NOMEM, "cudaMalloc(post-processing scratch): out of device memory");
+}
+
+// Loads this file's kernels onto the current device (a query of their attributes does it), so that the first hit
+// list of a client is not the one that pays for it. Called while the device is being opened.
+void havac_postprocess_preload() {
+  cudaFuncAttributes a;
+  cudaFuncGetAttributes(&a, hits_to_keys);
+  cudaFuncGetAttributes(&a, keys_to_hits);
+  cudaFuncGetAttributes(&a, radix_count);
+  cudaFuncGetAttributes(&a, scan_exclusive);
+  cudaFuncGetAttributes(&a, radix_scatter);
+  cudaFuncGetAttributes(&a, resolve_hits);
+  cudaGetLastError();
+}
 
 // Sorts the hitCount raw hits of device d into emission order, in place in d.dHits.
 int havac_sort_hits_on_device(havac_cuda_client* c, DeviceCtx& d) {
@@ -217,20 +248,9 @@ int havac_sort_hits_on_device(havac_cuda_client* c, DeviceCtx& d) {
   const size_t keysBytes = ((size_t)n * 8 + 255) & ~(size_t)255;
   const size_t countsBytes = ((size_t)256 * nBlocks * sizeof(unsigned) + 255) & ~(size_t)255;
   const size_t need = keysBytes + countsBytes + 256;
-  if (d.sortScratchCap < need) {
-    if (d.sortScratch) cudaFree(d.sortScratch);
-    d.sortScratch = nullptr;
-    d.sortScratchCap = 0;
-    const size_t want = need + need / 2;  // room to grow without another allocation
-    cudaError_t e = cudaMalloc(&d.sortScratch, want);
-    if (e != cudaSuccess) {
-      cudaGetLastError();
-      e = cudaMalloc(&d.sortScratch, need);
-      if (e != cudaSuccess) { cudaGetLastError(); return havac_fail(c, HAVAC_CUDA_E_NOMEM, "cudaMalloc(sort scratch): out of device memory"); }
-      d.sortScratchCap = need;
-    } else {
-      d.sortScratchCap = want;
-    }
+  {
+    const int rc = ensure_scratch(c, d, need);
+    if (rc) return rc;
   }
   unsigned char* const base = static_cast<unsigned char*>(d.sortScratch);
   unsigned long long* const dTmp = reinterpret_cast<unsigned long long*>(base);
@@ -291,20 +311,19 @@ extern "C" int havac_cuda_resolve_hits(havac_cuda_client* c, const uint64_t* seq
     if (rc) return rc;
     const auto t1 = now();
     CK(cudaSetDevice(d.dev));
-    Frees frees;
-    auto dalloc = [&](void** p, size_t bytes) {
-      cudaError_t e = cudaMalloc(p, bytes ? bytes : 16);
-      if (e == cudaSuccess) frees.p.push_back(*p);
-      return e;
-    };
-    unsigned long long *dEnd = nullptr, *dPos = nullptr;
-    unsigned *dPrefix = nullptr, *dSeqIdx = nullptr, *dPhmmPos = nullptr, *dPhmmIdx = nullptr;
-    CK(dalloc((void**)&dEnd, nSequences * 8));
-    CK(dalloc((void**)&dPrefix, (size_t)nModels * 4));
-    CK(dalloc((void**)&dPos, n * 8));
-    CK(dalloc((void**)&dSeqIdx, n * 4));
-    CK(dalloc((void**)&dPhmmPos, n * 4));
-    CK(dalloc((void**)&dPhmmIdx, n * 4));
+    // record ends, model prefix sums and the four result arrays, carved out of the context's scratch (256-byte parts)
+    auto part = [](size_t bytes) { return (bytes + 255) & ~(size_t)255; };
+    const size_t oEnd = 0, oPrefix = oEnd + part(nSequences * 8), oPos = oPrefix + part((size_t)nModels * 4), oSeqIdx = oPos + part(n * 8),
+                 oPhmmPos = oSeqIdx + part(n * 4), oPhmmIdx = oPhmmPos + part(n * 4), total = oPhmmIdx + part(n * 4);
+    rc = ensure_scratch(c, d, total);
+    if (rc) return rc;
+    unsigned char* const sb = static_cast<unsigned char*>(d.sortScratch);
+    unsigned long long* const dEnd = reinterpret_cast<unsigned long long*>(sb + oEnd);
+    unsigned* const dPrefix = reinterpret_cast<unsigned*>(sb + oPrefix);
+    unsigned long long* const dPos = reinterpret_cast<unsigned long long*>(sb + oPos);
+    unsigned* const dSeqIdx = reinterpret_cast<unsigned*>(sb + oSeqIdx);
+    unsigned* const dPhmmPos = reinterpret_cast<unsigned*>(sb + oPhmmPos);
+    unsigned* const dPhmmIdx = reinterpret_cast<unsigned*>(sb + oPhmmIdx);
     CK(cudaMemcpyAsync(dEnd, sequenceEnd, nSequences * 8, cudaMemcpyHostToDevice, d.stream));
     CK(cudaMemcpyAsync(dPrefix, prefix.data(), (size_t)nModels * 4, cudaMemcpyHostToDevice, d.stream));
     const unsigned grid = (unsigned)std::min<unsigned long long>((n + 255) / 256, 148ull * 16);
