@@ -97,7 +97,7 @@ def test_call_order_and_size_contracts():
 
 
 def test_abort_stops_a_long_run_and_reports_abort():
-    table, _ = synth.consensus_score_table(71, 60_000)
+    table, _ = synth.consensus_score_table(71, 150_000)  # 3e13 cells: about 0.9 s at 32 TCUPS
     packed = synth.random_packed(71, 200_000_000)
     c = HavacHwClient("")
     try:
@@ -109,7 +109,7 @@ def test_abort_stops_a_long_run_and_reports_abort():
         st = c.abort()
         dt = time.perf_counter() - t0
         assert st == STATE_ABORT and c.getHwState() == STATE_ABORT
-        assert dt < 0.3, f"abort took {dt:.3f} s; the full run is ~0.5 s"
+        assert dt < 0.3, f"abort took {dt:.3f} s; the full run is ~0.9 s"
         # and the client is usable again afterwards
         c.setKernel("f16x2")
         small = synth.random_packed(72, 12288 * 4)
