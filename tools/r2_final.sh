@@ -6,4 +6,4 @@ timeout 200 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')
 timeout 400 python bench.py > gpurun_out/r2_bench_final.json 2> gpurun_out/r2_bench_final.err; echo "bench rc=$?"
 grep "e2e wall" gpurun_out/r2_bench_final.err | cut -c1-400
 python -c "
-import json; d=json.load(open('gpurun_out/r2_bench_final.json')); print(d['value'], d['ms_per_step'], d['e2e']['value'], d['roofline']['frac'], d['roofline']['frac_at_kernel_clock'], d['strong']['value'])"
+import json; d=json.load(open('gpurun_out/r2_bench_final.json')); print(d['value'], d['ms_per_step'], d['e2e']['value'], d['roofline']['frac'], d['roofline']['first_cta_alive_share'], d['strong']['value'])"
