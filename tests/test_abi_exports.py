@@ -49,3 +49,32 @@ def test_product_never_touches_the_oracle():
             if f.endswith((".py", ".cpp", ".hpp", ".cu", ".cuh", ".h")):
                 text = open(os.path.join(base, f), errors="ignore").read()
                 assert "oracle_lib" not in text and "liboracle" not in text and "oracle/" not in text, f
+
+
+def test_no_alloc_sort_has_its_scratch_in_the_library_image():
+    """havac_cuda_sort_hits_static allocates nothing: its scratch is a file-scope device array of the library, of the
+    size include/havac_cuda.h promises (two key buffers of HAVAC_CUDA_SORT_STATIC_MAX_HITS words, the digit counts of
+    that many hits' tiles, one 256-byte slot), and the entry point's source names no allocating call."""
+    import shutil
+    import subprocess
+    build.build_all()
+    header = open(os.path.join(ROOT, "include", "havac_cuda.h")).read()
+    m = re.search(r"#define HAVAC_CUDA_SORT_STATIC_MAX_HITS \(1u << (\d+)\)", header)
+    assert m, "the header no longer states the maximum"
+    max_hits = 1 << int(m.group(1))
+    tile = 256 * 16  # STHREADS * ITEMS of hit_postprocess.cu
+    want = 2 * max_hits * 8 + 256 * (max_hits // tile) * 4 + 256
+    src = open(os.path.join(build.CSRC, "hit_postprocess.cu")).read()
+    body = src[src.index('extern "C" int havac_cuda_sort_hits_static'):]
+    body = body[:body.index("\n}\n") + 3]
+    for call in ("cudaMalloc", "cudaFree", "cudaHostAlloc", "cudaMallocAsync", "new ", "std::vector"):
+        assert call not in body, f"{call} inside the no-allocation entry point"
+    assert "cudaGetSymbolAddress" in src and "static __device__ __align__(256)" in src
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not installed")
+    ptx_or_elf = subprocess.run([cuobjdump, "-elf", build.CUDA_LIB], capture_output=True, text=True).stdout
+    sizes = [int(x) for x in re.findall(r"g_sortScratchE\[(\d+)\]", ptx_or_elf)]
+    if not sizes:  # no PTX in the image: take the symbol's size from the ELF symbol table instead
+        sizes = [int(x, 16) for x in re.findall(r"\s(0x[0-9a-f]+)\s+0x[0-9a-f]+\s+\d+\s+0x[0-9a-f]+\s+\S*g_sortScratchE", ptx_or_elf)]
+    assert sizes and all(s == want for s in sizes), (sizes, want)
